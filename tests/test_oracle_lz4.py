@@ -1,0 +1,102 @@
+"""Pins oracle/lz4_oracle.c at the LZ4 block format: liblz4 must decode the
+oracle encoder's output and the oracle decoder must decode liblz4's output
+(the reference holds no byte-level LZ4 vectors)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import datagen
+import oracle_lib as o
+
+_lz4 = C.CDLL("liblz4.so.1")
+_lz4.LZ4_compressBound.restype = C.c_int
+_lz4.LZ4_compress_default.restype = C.c_int
+_lz4.LZ4_compress_default.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+_lz4.LZ4_decompress_safe.restype = C.c_int
+_lz4.LZ4_decompress_safe.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+
+
+def stock_compress(raw):
+    raw = np.ascontiguousarray(raw)
+    out = np.zeros(_lz4.LZ4_compressBound(len(raw)) + 8, np.uint8)
+    n = _lz4.LZ4_compress_default(raw.ctypes.data, out.ctypes.data, len(raw), len(out))
+    assert n > 0 or len(raw) == 0
+    return out[:n].copy()
+
+
+def stock_decompress(comp, size):
+    comp = np.ascontiguousarray(comp)
+    out = np.zeros(max(size, 1), np.uint8)
+    n = _lz4.LZ4_decompress_safe(comp.ctypes.data, out.ctypes.data, len(comp), size)
+    return n, out[: max(n, 0)]
+
+
+@pytest.mark.parametrize("size", [1, 2, 4, 5, 12, 13, 14, 31, 32, 33, 45, 64, 255, 256, 1000, 4096, 65536, 70003])
+@pytest.mark.parametrize("tsize", [1, 2, 4])
+def test_cross_decode_with_liblz4(size, tsize):
+    for chunk in datagen.mixed_chunks(size, 6, 900 + size):
+        comp = o.lz4_compress(chunk, tsize, max_chunk=size)
+        assert len(comp) <= o.lz4_max_compressed(size)
+        n, out = stock_decompress(comp, size)
+        assert n == size and out.tobytes() == chunk.tobytes()
+        st, out = o.lz4_decompress(comp, size)
+        assert st == o.SUCCESS and out.tobytes() == chunk.tobytes()
+        st, n = o.lz4_decompress(comp, 0, write_output=False)
+        assert st == o.SUCCESS and n == size
+        stock = stock_compress(chunk)
+        st, out = o.lz4_decompress(stock, size)
+        assert st == o.SUCCESS and out.tobytes() == chunk.tobytes()
+
+
+def test_empty_chunk():
+    assert len(o.lz4_compress(np.zeros(0, np.uint8))) == 0
+    st, out = o.lz4_decompress(np.zeros(0, np.uint8), 0)
+    assert st == o.SUCCESS and len(out) == 0
+
+
+def test_last_token_low_nibble_matches_reference():
+    # the reference emits (0 - 4) & 0xF in the literal-only last token (LZ4Kernels.hiph:324-331)
+    comp = o.lz4_compress(np.arange(10, dtype=np.uint8))
+    assert comp[0] == (10 << 4) | 0xC
+
+
+def test_hash_table_size_rule():
+    assert o.lz4_hash_table_size(100) == 128
+    assert o.lz4_hash_table_size(4096) == 4096
+    assert o.lz4_hash_table_size(65536) == 16384
+    assert o.lz4_hash_table_size(1 << 24) == 16384
+    raw = datagen.log_lines(4096, 5)
+    a = o.lz4_compress(raw, 1, max_chunk=4096)
+    b = o.lz4_compress(raw, 1, max_chunk=65536)
+    for c in (a, b):
+        st, out = o.lz4_decompress(c, 4096)
+        assert st == o.SUCCESS and out.tobytes() == raw.tobytes()
+
+
+def test_decoder_error_conditions():
+    raw = datagen.log_lines(3000, 2)
+    comp = o.lz4_compress(raw)
+    assert o.lz4_decompress(comp, 2999)[0] == o.CANNOT_DECOMPRESS
+    st, out = o.lz4_decompress(comp, 2999)
+    assert len(out) == 0
+    # offset pointing before the start of the output
+    bad = bytes([0x10, ord("a"), 5, 0]) + bytes([0x50]) + b"bcdef"
+    assert o.lz4_decompress(bad, 100)[0] == o.CANNOT_DECOMPRESS
+    # offset 0
+    bad = bytes([0x40]) + b"abcd" + bytes([0, 0]) + bytes([0x50]) + b"bcdef"
+    assert o.lz4_decompress(bad, 100)[0] == o.CANNOT_DECOMPRESS
+    # raw ints as "compressed" data (reference corrupt-input test): never succeeds into size-1
+    rng = np.random.default_rng(0)
+    for _ in range(50):
+        junk = (rng.integers(0, 4, 300) + 300).astype(np.int32).view(np.uint8)
+        st, n = o.lz4_decompress(junk, 0, write_output=False)
+        cap = len(junk) if (st != o.SUCCESS or n == 0 or n > len(junk)) else n - 1
+        assert o.lz4_decompress(junk, cap)[0] == o.CANNOT_DECOMPRESS
+
+
+def test_ratio_close_to_liblz4():
+    raw = datagen.log_lines(1 << 20, 12)
+    ours = sum(len(o.lz4_compress(raw[i : i + 65536])) for i in range(0, len(raw), 65536))
+    stock = sum(len(stock_compress(raw[i : i + 65536])) for i in range(0, len(raw), 65536))
+    assert ours < 1.3 * stock
