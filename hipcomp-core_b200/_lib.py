@@ -1,0 +1,64 @@
+"""Loads libhipcomp.so (the sm_100a C-ABI library) and declares its 18 entry points.
+
+There is no CPU fallback: if the shared library is missing this raises.
+Build it with `python -c "import __graft_entry__ as g; g.build()"` or
+`make -C hipcomp-core_b200/csrc`.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libhipcomp.so")
+
+SUCCESS = 0
+ERROR_INVALID_VALUE = 10
+ERROR_NOT_SUPPORTED = 11
+ERROR_CANNOT_DECOMPRESS = 12
+ERROR_CUDA = 1000
+ERROR_INTERNAL = 10000
+
+TYPE_CHAR, TYPE_UCHAR, TYPE_SHORT, TYPE_USHORT, TYPE_INT, TYPE_UINT, TYPE_LONGLONG, TYPE_ULONGLONG = range(8)
+TYPE_BITS = 0xFF
+
+
+class LZ4Opts(C.Structure):
+    _fields_ = [("data_type", C.c_int)]
+
+
+class SnappyOpts(C.Structure):
+    _fields_ = [("reserved", C.c_int)]
+
+
+class CascadedOpts(C.Structure):
+    _fields_ = [("chunk_size", C.c_size_t), ("type", C.c_int), ("num_RLEs", C.c_int), ("num_deltas", C.c_int),
+                ("use_bp", C.c_int)]
+
+
+_sz, _vp, _szp = C.c_size_t, C.c_void_p, C.POINTER(C.c_size_t)
+
+# name -> argtypes (restype is always hipcompStatus_t == int); order as in include/hipcomp/*.h
+PROTOTYPES = {}
+for _c, _opts in (("LZ4", LZ4Opts), ("Snappy", SnappyOpts), ("Cascaded", CascadedOpts)):
+    PROTOTYPES[f"hipcompBatched{_c}CompressGetTempSize"] = [_sz, _sz, _opts, _szp]
+    PROTOTYPES[f"hipcompBatched{_c}CompressGetMaxOutputChunkSize"] = [_sz, _opts, _szp]
+    PROTOTYPES[f"hipcompBatched{_c}CompressAsync"] = [_vp, _vp, _sz, _sz, _vp, _sz, _vp, _vp, _opts, _vp]
+    PROTOTYPES[f"hipcompBatched{_c}DecompressGetTempSize"] = [_sz, _sz, _szp]
+    PROTOTYPES[f"hipcompBatched{_c}DecompressAsync"] = [_vp, _vp, _vp, _vp, _sz, _vp, _sz, _vp, _vp, _vp]
+    PROTOTYPES[f"hipcompBatched{_c}GetDecompressSizeAsync"] = [_vp, _vp, _vp, _sz, _vp]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: the CUDA library has not been built "
+                "(run __graft_entry__.build()). There is no CPU fallback.")
+        _lib = C.CDLL(LIB_PATH)
+        for name, args in PROTOTYPES.items():
+            fn = getattr(_lib, name)
+            fn.restype = C.c_int
+            fn.argtypes = args
+    return _lib

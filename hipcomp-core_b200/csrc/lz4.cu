@@ -1,0 +1,403 @@
+// b200comp — batched LZ4 block codec for sm_100a.
+//
+// C ABI replaces reference src/lowlevel/LZ4Batch.cpp:71-224; the encoder keeps the
+// reference's greedy match policy (src/LZ4Kernels.hiph:793-969: 32-position
+// window, intra-window twins, uint16 hash table with last-lane-wins insertion) so
+// that its output is the same byte stream, and changes the data movement: the
+// hash table lives in shared memory (the reference keeps 32 KiB per chunk in
+// global memory and re-initialises it through L2), window keys come from two
+// aligned word loads + funnel shift instead of byte loads and shuffles, and
+// literal runs move as 16-byte vectors.  The decoder bounds every compressed
+// read (the reference's does not).
+#include "lz_common.cuh"
+
+#pragma GCC visibility push(default)
+#include "hipcomp/lz4.h"
+#pragma GCC visibility pop
+
+namespace b200comp {
+namespace lz4 {
+
+constexpr uint32_t kNullOffset = 0xFFFFu;
+constexpr uint32_t kMaxOffset = 65535u;
+constexpr size_t kMaxChunk = 1u << 24;
+constexpr uint32_t kMaxHashTable = 1u << 14;
+
+static size_t hash_table_size(size_t max_chunk)
+{
+  size_t p = 1;
+  while (p < max_chunk) p *= 2;
+  return p < kMaxHashTable ? p : kMaxHashTable;
+}
+
+static size_t max_compressed(size_t n) { return round_up_sz(n + 1 + (n + 254) / 255, 8); }
+
+__device__ __forceinline__ uint32_t hash_key(uint32_t key, uint32_t ht) { return (__brev(key) + (key ^ 0xc375u)) & (ht - 1); }
+
+// length-in-sequence-of-0xFF encoding, written cooperatively
+__device__ __forceinline__ uint32_t put_lsic(uint8_t* out, uint32_t x)
+{
+  const uint32_t num = x / 255u + 1u;
+  for (uint32_t i = (uint32_t)lane_id(); i < num; i += 32) out[i] = (i + 1 < num) ? (uint8_t)0xff : (uint8_t)(x % 255u);
+  return num;
+}
+
+// token, literal length, literals, offset, match length (LZ4Kernels.hiph:665-715)
+__device__ __forceinline__ uint32_t put_sequence(uint8_t* out, uint32_t c, const uint8_t* lit, uint32_t nlit,
+                                                 uint32_t nmatch, uint32_t offset)
+{
+  if (lane_id() == 0) {
+    const uint32_t hi = nlit >= 15 ? 15u : nlit;
+    const uint32_t lo = nmatch >= 19 ? 15u : ((nmatch - 4u) & 0x0fu); // (0-4)&15 on the last token, as the reference
+    out[c] = (uint8_t)((hi << 4) | lo);
+  }
+  ++c;
+  if (nlit >= 15) c += put_lsic(out + c, nlit - 15);
+  warp_copy_ro(out + c, lit, nlit);
+  c += nlit;
+  if (nmatch > 0) {
+    if (lane_id() == 0) {
+      out[c] = (uint8_t)(offset & 0xff);
+      out[c + 1] = (uint8_t)(offset >> 8);
+    }
+    c += 2;
+    if (nmatch >= 19) c += put_lsic(out + c, nmatch - 19);
+  }
+  return c;
+}
+
+// One warp per chunk.  TS = match granularity in bytes (data_type width).
+template <int TS>
+__global__ void __launch_bounds__(32)
+compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
+                size_t batch, uint32_t ht_size)
+{
+  extern __shared__ __align__(16) uint16_t table[];
+  const uint32_t lane = (uint32_t)lane_id();
+  constexpr uint32_t last_valid_match = (12 + TS - 1) / TS;
+  constexpr uint32_t min_ending = (5 + TS - 1) / TS;
+  constexpr uint32_t window = 32 - 3 / TS;
+
+  for (size_t chunk = blockIdx.x; chunk < batch; chunk += gridDim.x) {
+    const uint8_t* in = static_cast<const uint8_t*>(in_ptrs[chunk]);
+    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t length = (uint32_t)in_bytes[chunk];
+    const uint32_t typed_length = (length + TS - 1) / TS;
+
+    {
+      uint32_t* t32 = reinterpret_cast<uint32_t*>(table);
+      for (uint32_t i = lane; i < (ht_size + 1) / 2; i += 32) t32[i] = 0xFFFFFFFFu;
+    }
+    __syncwarp();
+
+    uint32_t d = 0, c = 0;
+    while (d < typed_length) {
+      const uint32_t token_start = d;
+      for (;;) {
+        if (d + last_valid_match >= typed_length) {
+          c = put_sequence(out, c, in + (size_t)token_start * TS, length - token_start * TS, 0, 0);
+          d = typed_length;
+          break;
+        }
+        const uint32_t nvalid = min(window, typed_length - d - last_valid_match);
+        const unsigned vmask = nvalid >= 32 ? kFull : ((1u << nvalid) - 1u);
+        const bool valid = lane < nvalid;
+        const uint32_t key = valid ? ld_unaligned32_ro(in + (size_t)(d + lane) * TS) : 0u;
+
+        // (1) earliest lane that repeats the key of a lower lane in this window
+        unsigned same = 0;
+        if (valid) same = __match_any_sync(vmask, key);
+        const uint32_t lowest = same ? (uint32_t)__ffs((int)same) - 1u : lane;
+        const unsigned twins = __ballot_sync(kFull, valid && lowest != lane);
+        uint32_t first = nvalid;
+        uint32_t match_loc = typed_length;
+        if (twins) {
+          first = (uint32_t)__ffs((int)twins) - 1u;
+          match_loc = d + __shfl_sync(kFull, lowest, (int)first);
+        }
+        // (2) lanes in front of it probe the table
+        const uint32_t hpos = hash_key(key, ht_size);
+        bool found = false;
+        uint32_t cand = 0;
+        if (lane < first) {
+          const uint32_t h = table[hpos];
+          if (h != kNullOffset) {
+            const uint32_t pos = d + lane;
+            cand = (pos & ~kMaxOffset) + h;
+            if (cand >= pos) cand -= 65536u;
+            const uint32_t dist = pos - cand;
+            if (cand < pos && dist <= kMaxOffset && dist * TS <= kMaxOffset)
+              found = ld_unaligned32_ro(in + (size_t)cand * TS) == key;
+          }
+        }
+        const unsigned hits = __ballot_sync(kFull, found);
+        if (hits) {
+          first = (uint32_t)__ffs((int)hits) - 1u;
+          match_loc = __shfl_sync(kFull, cand, (int)first);
+        }
+        // (3) insert the lanes in front of the match (all valid lanes when there
+        //     is none); the highest lane wins a contended slot
+        const uint32_t ninsert = match_loc != typed_length ? first : nvalid;
+        if (lane < ninsert) {
+          const unsigned imask = ninsert >= 32 ? kFull : ((1u << ninsert) - 1u);
+          const unsigned grp = __match_any_sync(imask, hpos);
+          if (31u - (uint32_t)__clz((int)grp) == lane) table[hpos] = (uint16_t)((d + lane) & kMaxOffset);
+        }
+        __syncwarp();
+        if (match_loc == typed_length) {
+          d += nvalid;
+          continue;
+        }
+        // (4) extend the match, 32 elements per step
+        const uint32_t pos = d + first;
+        const uint32_t limit = typed_length - pos - min_ending;
+        uint32_t mlen = limit;
+        for (uint32_t j = 0; j < limit; j += 32) {
+          const uint32_t i = j + lane;
+          bool neq = true;
+          if (i < limit) {
+            if (TS == 1)
+              neq = __ldg(in + match_loc + i) != __ldg(in + pos + i);
+            else if (TS == 2)
+              neq = __ldg(reinterpret_cast<const uint16_t*>(in) + match_loc + i)
+                    != __ldg(reinterpret_cast<const uint16_t*>(in) + pos + i);
+            else
+              neq = __ldg(reinterpret_cast<const uint32_t*>(in) + match_loc + i)
+                    != __ldg(reinterpret_cast<const uint32_t*>(in) + pos + i);
+          }
+          const unsigned diff = __ballot_sync(kFull, neq);
+          if (diff) {
+            mlen = j + (uint32_t)__ffs((int)diff) - 1u;
+            break;
+          }
+        }
+        const uint32_t nlit = pos - token_start;
+        c = put_sequence(out, c, in + (size_t)token_start * TS, nlit * TS, mlen * TS, (pos - match_loc) * TS);
+        d = token_start + nlit + mlen;
+        break;
+      }
+    }
+    if (lane == 0) out_bytes[chunk] = c;
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------ decode
+
+constexpr int kDecWarps = 4;
+
+__device__ __forceinline__ bool read_lsic(const uint8_t* comp, uint32_t comp_len, uint32_t& ci, uint32_t& value)
+{
+  uint32_t b = 0xff;
+  while (b == 0xff) {
+    if (ci >= comp_len) return false;
+    b = __ldg(comp + ci);
+    ++ci;
+    value += b;
+  }
+  return true;
+}
+
+// One warp per chunk; every lane parses the (broadcast) token stream, copies are
+// cooperative.  (reference decompressStream, LZ4Kernels.hiph:971-1097)
+__global__ void __launch_bounds__(kDecWarps * 32)
+decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
+                  void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
+{
+  const size_t stride = (size_t)gridDim.x * kDecWarps;
+  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    const size_t cap64 = out_caps[chunk];
+    const uint32_t cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
+    uint32_t ci = 0, di = 0;
+    bool ok = true;
+    while (ci < comp_len) {
+      const uint32_t tok = __ldg(comp + ci);
+      ++ci;
+      uint32_t nlit = tok >> 4;
+      if (nlit == 15 && !read_lsic(comp, comp_len, ci, nlit)) { ok = false; break; }
+      if (nlit > cap - di || nlit > comp_len - ci) { ok = false; break; }
+      warp_copy_ro(out + di, comp + ci, nlit);
+      ci += nlit;
+      di += nlit;
+      if (ci < comp_len) {
+        if (ci + 2 > comp_len) { ok = false; break; }
+        const uint32_t off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
+        ci += 2;
+        uint32_t mlen = 4 + (tok & 15);
+        if ((tok & 15) == 15 && !read_lsic(comp, comp_len, ci, mlen)) { ok = false; break; }
+        if (off == 0 || off > di || mlen > cap - di) { ok = false; break; }
+        __syncwarp();
+        warp_copy_match(out + di, off, mlen);
+        di += mlen;
+        __syncwarp();
+      }
+    }
+    if (lane_id() == 0) {
+      if (actual) actual[chunk] = ok ? di : 0;
+      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
+    }
+    __syncwarp();
+  }
+}
+
+// Size-only walk: one thread per chunk.
+__global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, size_t* sizes, size_t batch)
+{
+  for (size_t chunk = (size_t)blockIdx.x * blockDim.x + threadIdx.x; chunk < batch;
+       chunk += (size_t)gridDim.x * blockDim.x) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    uint32_t ci = 0;
+    unsigned long long di = 0;
+    bool ok = true;
+    while (ci < comp_len) {
+      const uint32_t tok = comp[ci++];
+      uint32_t nlit = tok >> 4;
+      if (nlit == 15 && !read_lsic(comp, comp_len, ci, nlit)) { ok = false; break; }
+      if (nlit > comp_len - ci) { ok = false; break; }
+      ci += nlit;
+      di += nlit;
+      if (ci < comp_len) {
+        if (ci + 2 > comp_len) { ok = false; break; }
+        const uint32_t off = (uint32_t)comp[ci] | ((uint32_t)comp[ci + 1] << 8);
+        ci += 2;
+        uint32_t mlen = 4 + (tok & 15);
+        if ((tok & 15) == 15 && !read_lsic(comp, comp_len, ci, mlen)) { ok = false; break; }
+        if (off == 0 || off > di) { ok = false; break; }
+        di += mlen;
+      }
+      if (di > 0xFFFFFFFFull) { ok = false; break; }
+    }
+    sizes[chunk] = ok ? (size_t)di : 0;
+  }
+}
+
+} // namespace lz4
+} // namespace b200comp
+
+using namespace b200comp;
+
+extern "C" {
+
+hipcompStatus_t hipcompBatchedLZ4CompressGetTempSize(size_t batch_size, size_t max_uncompressed_chunk_bytes,
+                                                     hipcompBatchedLZ4Opts_t, size_t* temp_bytes)
+{
+  static const char* fn = "hipcompBatchedLZ4CompressGetTempSize()";
+  B200_CHECK_NOT_NULL(temp_bytes, fn);
+  if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
+    return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
+  // Same figure as the reference so callers' allocations stay valid; the hash
+  // tables themselves live in shared memory and the workspace is not touched.
+  *temp_bytes = lz4::hash_table_size(max_uncompressed_chunk_bytes) * sizeof(uint16_t) * batch_size;
+  return hipcompSuccess;
+}
+
+hipcompStatus_t hipcompBatchedLZ4CompressGetMaxOutputChunkSize(size_t max_uncompressed_chunk_bytes,
+                                                               hipcompBatchedLZ4Opts_t, size_t* max_compressed_bytes)
+{
+  static const char* fn = "hipcompBatchedLZ4CompressGetOutputSize()";
+  B200_CHECK_NOT_NULL(max_compressed_bytes, fn);
+  if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
+    return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
+  *max_compressed_bytes = lz4::max_compressed(max_uncompressed_chunk_bytes);
+  return hipcompSuccess;
+}
+
+hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompressed_ptrs,
+                                               const size_t* device_uncompressed_bytes,
+                                               size_t max_uncompressed_chunk_bytes, size_t batch_size,
+                                               void* device_temp_ptr, size_t temp_bytes,
+                                               void* const* device_compressed_ptrs, size_t* device_compressed_bytes,
+                                               hipcompBatchedLZ4Opts_t format_opts, hipStream_t stream)
+{
+  static const char* fn = "hipcompBatchedLZ4CompressAsync()";
+  (void)device_temp_ptr;
+  if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
+    return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
+  const uint32_t ht = (uint32_t)lz4::hash_table_size(max_uncompressed_chunk_bytes);
+  const size_t required = batch_size * ht * sizeof(uint16_t);
+  if (temp_bytes < required)
+    return fail(hipcompErrorInvalidValue, fn,
+                "Insufficient temp space: got " + std::to_string(temp_bytes) + " bytes, but need "
+                    + std::to_string(required) + " bytes.");
+  if (batch_size == 0) return hipcompSuccess;
+  B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  const int smem = (int)(((ht + 1) / 2) * 4);
+  const int per_sm = smem >= 32768 ? 6 : (smem >= 16384 ? 12 : (smem >= 8192 ? 24 : 32));
+  const size_t cap = (size_t)sm_count() * per_sm;
+  const int grid = (int)(batch_size < cap ? batch_size : cap);
+  switch (format_opts.data_type) {
+  case HIPCOMP_TYPE_BITS:
+  case HIPCOMP_TYPE_CHAR:
+  case HIPCOMP_TYPE_UCHAR:
+    lz4::compress_kernel<1><<<grid, 32, smem, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes,
+                                                        device_compressed_ptrs, device_compressed_bytes, batch_size, ht);
+    break;
+  case HIPCOMP_TYPE_SHORT:
+  case HIPCOMP_TYPE_USHORT:
+    lz4::compress_kernel<2><<<grid, 32, smem, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes,
+                                                        device_compressed_ptrs, device_compressed_bytes, batch_size, ht);
+    break;
+  case HIPCOMP_TYPE_INT:
+  case HIPCOMP_TYPE_UINT:
+    lz4::compress_kernel<4><<<grid, 32, smem, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes,
+                                                        device_compressed_ptrs, device_compressed_bytes, batch_size, ht);
+    break;
+  default:
+    return fail(hipcompErrorInvalidValue, fn, "Unsupported input data type");
+  }
+  return check_launch(fn);
+}
+
+hipcompStatus_t hipcompBatchedLZ4DecompressGetTempSize(size_t num_chunks, size_t, size_t* temp_bytes)
+{
+  B200_CHECK_NOT_NULL(temp_bytes, "hipcompBatchedLZ4DecompressGetTempSize()");
+  *temp_bytes = round_up_sz(24 * num_chunks, 8);
+  return hipcompSuccess;
+}
+
+hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compressed_ptrs,
+                                                 const size_t* device_compressed_bytes,
+                                                 const size_t* device_uncompressed_bytes,
+                                                 size_t* device_actual_uncompressed_bytes, size_t batch_size,
+                                                 void* const, size_t, void* const* device_uncompressed_ptrs,
+                                                 hipcompStatus_t* device_statuses, hipStream_t stream)
+{
+  static const char* fn = "hipcompBatchedLZ4DecompressAsync()";
+  if (batch_size == 0) return hipcompSuccess;
+  B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
+  const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
+  const size_t cap = (size_t)sm_count() * 16;
+  lz4::decompress_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
+      device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
+      device_actual_uncompressed_bytes, device_statuses, batch_size);
+  return check_launch(fn);
+}
+
+hipcompStatus_t hipcompBatchedLZ4GetDecompressSizeAsync(const void* const* device_compressed_ptrs,
+                                                        const size_t* device_compressed_bytes,
+                                                        size_t* device_uncompressed_bytes, size_t batch_size,
+                                                        hipStream_t stream)
+{
+  static const char* fn = "hipcompBatchedLZ4GetDecompressSizeAsync()";
+  B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  if (batch_size == 0) return hipcompSuccess;
+  const size_t need = (batch_size + 127) / 128;
+  const size_t cap = (size_t)sm_count() * 16;
+  lz4::size_kernel<<<(int)(need < cap ? need : cap), 128, 0, stream>>>(device_compressed_ptrs, device_compressed_bytes,
+                                                                       device_uncompressed_bytes, batch_size);
+  return check_launch(fn);
+}
+
+} // extern "C"

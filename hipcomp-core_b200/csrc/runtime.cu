@@ -1,0 +1,22 @@
+// b200comp — small runtime utilities shared by the codecs.
+#include "common.cuh"
+
+#include <atomic>
+
+namespace b200comp {
+
+int sm_count()
+{
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  int v = cache[dev].load(std::memory_order_relaxed);
+  if (v == 0) {
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    cache[dev].store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
+} // namespace b200comp

@@ -1,0 +1,361 @@
+// b200comp — batched Snappy raw-block codec for sm_100a.
+//
+// C ABI replaces reference src/lowlevel/SnappyBatch.cpp:84-245.  The encoder keeps
+// the reference's match policy (src/snappy/compression.hiph:190-385: 12-bit hash,
+// 32-position windows, nearest-lower-lane twin, uint16 table, <=64-byte copies)
+// so its output is the same byte stream, but one warp does search and emission
+// back to back (the reference ping-pongs two warps through __syncthreads()), and
+// several chunks share a CTA.  The decoder is one warp per chunk over the
+// element grammar of src/snappy/decompression_decode.hiph:72-150 (the reference
+// uses a 3-warp prefetch/decode/process pipeline with nanosleep spin queues).
+#include "lz_common.cuh"
+
+#pragma GCC visibility push(default)
+#include "hipcomp/snappy.h"
+#pragma GCC visibility pop
+
+namespace b200comp {
+namespace snappy {
+
+constexpr uint32_t kHashBits = 12;
+constexpr uint32_t kMaxLiteral = 256;
+constexpr uint32_t kMaxCopyDistance = 32768;
+constexpr int kCompWarps = 4;
+constexpr int kDecWarps = 4;
+
+__device__ __forceinline__ uint32_t snap_hash(uint32_t v) { return (v * 0x102A6Bu) >> (32 - kHashBits); }
+
+// literal element header + bytes (compression.hiph:73-117)
+__device__ __forceinline__ uint32_t put_literal(uint8_t* dst, uint32_t o, const uint8_t* src, uint32_t len)
+{
+  const uint32_t l1 = len - 1;
+  uint32_t hdr;
+  if (l1 < 60) hdr = 1;
+  else if (l1 <= 0xff) hdr = 2;
+  else if (l1 <= 0xffff) hdr = 3;
+  else if (l1 <= 0xffffff) hdr = 4;
+  else hdr = 5;
+  if (lane_id() == 0) {
+    if (hdr == 1) {
+      dst[o] = (uint8_t)(l1 << 2);
+    } else {
+      dst[o] = (uint8_t)((58 + hdr) << 2);
+      for (uint32_t i = 0; i + 1 < hdr; ++i) dst[o + 1 + i] = (uint8_t)(l1 >> (8 * i));
+    }
+  }
+  o += hdr;
+  warp_copy_ro(dst + o, src, len);
+  return o + len;
+}
+
+// copy element (compression.hiph:129-151)
+__device__ __forceinline__ uint32_t put_copy(uint8_t* dst, uint32_t o, uint32_t len, uint32_t dist)
+{
+  if (len < 12 && dist < 2048) {
+    if (lane_id() == 0) {
+      dst[o] = (uint8_t)(((dist & 0x700) >> 3) | ((len - 4) << 2) | 0x01);
+      dst[o + 1] = (uint8_t)dist;
+    }
+    return o + 2;
+  }
+  if (lane_id() == 0) {
+    dst[o] = (uint8_t)(((len - 1) << 2) | 0x2);
+    dst[o + 1] = (uint8_t)dist;
+    dst[o + 2] = (uint8_t)(dist >> 8);
+  }
+  return o + 3;
+}
+
+__global__ void __launch_bounds__(kCompWarps * 32)
+compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
+                size_t batch)
+{
+  __shared__ uint16_t maps[kCompWarps][1 << kHashBits];
+  const uint32_t lane = (uint32_t)lane_id();
+  const int warp = threadIdx.x >> 5;
+  uint16_t* map = maps[warp];
+  const unsigned lt = lanemask_lt();
+  const size_t stride = (size_t)gridDim.x * kCompWarps;
+
+  for (size_t chunk = (size_t)blockIdx.x * kCompWarps + warp; chunk < batch; chunk += stride) {
+    const uint8_t* src = static_cast<const uint8_t*>(in_ptrs[chunk]);
+    uint8_t* dst = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t len = (uint32_t)in_bytes[chunk];
+    {
+      uint32_t* m32 = reinterpret_cast<uint32_t*>(map);
+      for (uint32_t i = lane; i < (1u << kHashBits) / 2; i += 32) m32[i] = 0;
+    }
+    uint32_t o = 0;
+    if (lane == 0) {
+      uint32_t v = len;
+      while (v > 0x7f) { dst[o++] = (uint8_t)(v | 0x80); v >>= 7; }
+      dst[o++] = (uint8_t)v;
+    }
+    o = __shfl_sync(kFull, o, 0);
+    __syncwarp();
+
+    uint32_t pos = 0;
+    while (pos < len) {
+      // ---- search round: up to 8 windows of 32 positions (FindFourByteMatch)
+      uint32_t p = pos;
+      const uint32_t maxpos = pos + kMaxLiteral - 31;
+      uint32_t literal_cnt;
+      uint32_t copy_len = 0, dist = 0;
+      do {
+        const bool valid4 = p + lane + 4 <= len;
+        const uint32_t data = valid4 ? ld_unaligned32_ro(src + p + lane) : 0u;
+        const uint32_t hash = valid4 ? snap_hash(data) : 0u;
+        const unsigned group = __match_any_sync(kFull, hash);
+        const unsigned lower = group & lt;
+        const uint32_t lower_lane = lower ? 31u - (uint32_t)__clz((int)lower) : lane;
+        const uint32_t lower_data = __shfl_sync(kFull, data, (int)lower_lane);
+        uint32_t offset = p + lane;
+        bool match = false;
+        if (valid4) {
+          if (lower && lower_data == data) {
+            match = true;
+            offset = p + lower_lane;
+          } else {
+            offset = (p & ~0xffffu) | map[hash];
+            if (offset >= p) offset = offset >= 0x10000u ? offset - 0x10000u : p;
+            match = offset < p && offset + kMaxCopyDistance >= p + lane && ld_unaligned32_ro(src + offset) == data;
+          }
+        }
+        const unsigned mm = __ballot_sync(kFull, match);
+        if (mm) {
+          literal_cnt = (uint32_t)__ffs((int)mm) - 1u;
+          dist = p + literal_cnt - __shfl_sync(kFull, offset, (int)literal_cnt);
+          copy_len = 4;
+        } else {
+          literal_cnt = 32;
+        }
+        // table update: highest lane of each equal-hash group among lanes <= literal_cnt
+        const unsigned keep = literal_cnt >= 31 ? kFull : ((2u << literal_cnt) - 1u);
+        const unsigned g = valid4 ? (group & keep) : 0u;
+        if (lane <= literal_cnt && g && 31u - (uint32_t)__clz((int)g) == lane) map[hash] = (uint16_t)(p + lane);
+        __syncwarp();
+        p += literal_cnt;
+      } while (literal_cnt == 32 && p < maxpos);
+      const uint32_t lit = min(p, len) - pos;
+      // ---- extend the 4-byte match by up to 60 bytes (Match60)
+      if (copy_len) {
+        const uint32_t mpos = pos + lit + 4;
+        const uint32_t lim = min(len - mpos, 60u);
+        const bool ne0 = lane >= lim || __ldg(src + mpos + lane) != __ldg(src + mpos - dist + lane);
+        const unsigned m0 = __ballot_sync(kFull, ne0);
+        if (m0) {
+          copy_len += (uint32_t)__ffs((int)m0) - 1u;
+        } else {
+          const bool ne1 = 32 + lane >= lim || __ldg(src + mpos + 32 + lane) != __ldg(src + mpos - dist + 32 + lane);
+          const unsigned m1 = __ballot_sync(kFull, ne1);
+          copy_len += 31u + (uint32_t)__ffs((int)m1);
+        }
+      }
+      // ---- emit
+      if (lit) o = put_literal(dst, o, src + pos, lit);
+      pos += lit;
+      if (copy_len) o = put_copy(dst, o, copy_len, dist);
+      pos += copy_len;
+    }
+    if (lane == 0) out_bytes[chunk] = o;
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------ decode
+
+// varint preamble; bytes past the end read as 0, fifth byte >= 8 is an error
+// (SnappyBatchKernels.hip:84-134, decompression.hiph:71-104)
+__device__ __forceinline__ bool read_preamble(const uint8_t* comp, uint32_t comp_len, uint32_t& cur, uint32_t& size)
+{
+  size = 0;
+  cur = 0;
+#pragma unroll
+  for (int shift = 0; shift <= 28; shift += 7) {
+    const uint32_t c = cur < comp_len ? (uint32_t)__ldg(comp + cur) : 0u;
+    if (cur < comp_len) ++cur;
+    if (shift == 28) {
+      if (c >= 8) return false;
+      size |= c << 28;
+      break;
+    }
+    size |= (c & 0x7f) << shift;
+    if (!(c & 0x80)) break;
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(kDecWarps * 32)
+decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
+                  void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
+{
+  const size_t stride = (size_t)gridDim.x * kDecWarps;
+  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    const size_t cap64 = out_caps[chunk];
+    uint32_t size = 0, cur = 0, left = 0;
+    bool ok = comp_len != 0 && comp != nullptr;
+    if (ok) ok = read_preamble(comp, comp_len, cur, size);
+    if (ok) {
+      const size_t cap = cap64 == 0 ? size : cap64; // 0 = "trust the preamble" (decompression.hiph:148-149)
+      if ((cur >= comp_len && size != 0) || size > cap) ok = false;
+    }
+    if (ok) {
+      left = size;
+      uint32_t dst = 0;
+      while (left > 0) {
+        if (cur >= comp_len) { ok = false; break; }
+        const uint32_t b0 = __ldg(comp + cur);
+        uint32_t blen;
+        if (b0 & 3) {
+          uint32_t offset;
+          if ((b0 & 3) == 1) {
+            if (cur + 2 > comp_len) { ok = false; break; }
+            offset = ((b0 & 0xe0) << 3) | __ldg(comp + cur + 1);
+            blen = ((b0 >> 2) & 7) + 4;
+            cur += 2;
+          } else if ((b0 & 3) == 2) {
+            if (cur + 3 > comp_len) { ok = false; break; }
+            offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8);
+            blen = (b0 >> 2) + 1;
+            cur += 3;
+          } else {
+            if (cur + 5 > comp_len) { ok = false; break; }
+            offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8)
+                     | ((uint32_t)__ldg(comp + cur + 3) << 16) | ((uint32_t)__ldg(comp + cur + 4) << 24);
+            blen = (b0 >> 2) + 1;
+            cur += 5;
+          }
+          if (offset == 0 || offset > dst || left < blen) { ok = false; break; }
+          __syncwarp();
+          warp_copy_match(out + dst, offset, blen);
+          __syncwarp();
+        } else {
+          blen = b0 >> 2;
+          cur += 1;
+          if (blen >= 60) {
+            const uint32_t nb = blen - 59;
+            if (cur + nb > comp_len) { ok = false; break; }
+            blen = 0;
+            for (uint32_t i = 0; i < nb; ++i) blen |= (uint32_t)__ldg(comp + cur + i) << (8 * i);
+            cur += nb;
+          }
+          if (blen == 0xffffffffu) { ok = false; break; }
+          blen += 1;
+          if (left < blen || blen > comp_len - cur) { ok = false; break; }
+          warp_copy_ro(out + dst, comp + cur, blen);
+          cur += blen;
+        }
+        dst += blen;
+        left -= blen;
+      }
+    }
+    if (lane_id() == 0) {
+      if (actual) actual[chunk] = size - left;
+      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, size_t* sizes, size_t batch)
+{
+  for (size_t chunk = (size_t)blockIdx.x * blockDim.x + threadIdx.x; chunk < batch;
+       chunk += (size_t)gridDim.x * blockDim.x) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    uint32_t cur, size = 0;
+    if (comp_len == 0 || comp == nullptr || !read_preamble(comp, comp_len, cur, size)) size = 0;
+    sizes[chunk] = size;
+  }
+}
+
+} // namespace snappy
+} // namespace b200comp
+
+using namespace b200comp;
+
+extern "C" {
+
+hipcompStatus_t hipcompBatchedSnappyDecompressGetTempSize(size_t, size_t, size_t* temp_bytes)
+{
+  B200_CHECK_NOT_NULL(temp_bytes, "hipcompBatchedSnappyDecompressGetTempSize()");
+  *temp_bytes = 0;
+  return hipcompSuccess;
+}
+
+hipcompStatus_t hipcompBatchedSnappyGetDecompressSizeAsync(const void* const* device_compressed_ptrs,
+                                                           const size_t* device_compressed_bytes,
+                                                           size_t* device_uncompressed_bytes, size_t batch_size,
+                                                           hipStream_t stream)
+{
+  static const char* fn = "hipcompBatchedSnappyGetDecompressSizeAsync()";
+  B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  if (batch_size == 0) return hipcompSuccess;
+  const size_t need = (batch_size + 127) / 128;
+  const size_t cap = (size_t)sm_count() * 16;
+  snappy::size_kernel<<<(int)(need < cap ? need : cap), 128, 0, stream>>>(
+      device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, batch_size);
+  return check_launch(fn);
+}
+
+hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_compresed_ptrs,
+                                                    const size_t* device_compressed_bytes,
+                                                    const size_t* device_uncompressed_bytes,
+                                                    size_t* device_actual_uncompressed_bytes, size_t batch_size,
+                                                    void* const, const size_t, void* const* device_uncompressed_ptr,
+                                                    hipcompStatus_t* device_statuses, hipStream_t stream)
+{
+  static const char* fn = "hipcompBatchedSnappyDecompressAsync()";
+  B200_CHECK_NOT_NULL(device_compresed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
+  if (batch_size == 0) return hipcompSuccess;
+  const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
+  const size_t cap = (size_t)sm_count() * 16;
+  snappy::decompress_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
+      device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
+      device_actual_uncompressed_bytes, device_statuses, batch_size);
+  return check_launch(fn);
+}
+
+hipcompStatus_t hipcompBatchedSnappyCompressGetTempSize(size_t, size_t, hipcompBatchedSnappyOpts_t, size_t* temp_bytes)
+{
+  B200_CHECK_NOT_NULL(temp_bytes, "hipcompBatchedSnappyCompressGetTempSize()");
+  *temp_bytes = 0;
+  return hipcompSuccess;
+}
+
+hipcompStatus_t hipcompBatchedSnappyCompressGetMaxOutputChunkSize(size_t max_chunk_size, hipcompBatchedSnappyOpts_t,
+                                                                  size_t* max_compressed_size)
+{
+  B200_CHECK_NOT_NULL(max_compressed_size, "hipcompBatchedSnappyCompressGetOutputSize()");
+  *max_compressed_size = 32 + max_chunk_size + max_chunk_size / 6;
+  return hipcompSuccess;
+}
+
+hipcompStatus_t hipcompBatchedSnappyCompressAsync(const void* const* device_uncompressed_ptr,
+                                                  const size_t* device_uncompressed_bytes, size_t, size_t batch_size,
+                                                  void*, size_t, void* const* device_compressed_ptr,
+                                                  size_t* device_compressed_bytes, hipcompBatchedSnappyOpts_t,
+                                                  hipStream_t stream)
+{
+  static const char* fn = "hipcompBatchedSnappyCompressAsync()";
+  B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_compressed_ptr, fn);
+  B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  if (batch_size == 0) return hipcompSuccess;
+  const size_t need = (batch_size + snappy::kCompWarps - 1) / snappy::kCompWarps;
+  const size_t cap = (size_t)sm_count() * 6;
+  snappy::compress_kernel<<<(int)(need < cap ? need : cap), snappy::kCompWarps * 32, 0, stream>>>(
+      device_uncompressed_ptr, device_uncompressed_bytes, device_compressed_ptr, device_compressed_bytes, batch_size);
+  return check_launch(fn);
+}
+
+} // extern "C"

@@ -1,0 +1,219 @@
+"""-m gpu parity tests: the CUDA path through the C ABI vs the CPU oracle (bit-exact)."""
+import numpy as np
+import pytest
+import torch
+
+import datagen
+import oracle_lib as o
+
+pytestmark = pytest.mark.gpu
+
+DTYPES = {0: np.int8, 1: np.uint8, 2: np.int16, 3: np.uint16, 4: np.int32, 5: np.uint32, 6: np.int64, 7: np.uint64}
+
+
+def _g():
+    import gpu_common
+
+    return gpu_common
+
+
+def ragged_chunks(max_size, n, seed):
+    rng = np.random.default_rng(seed)
+    base = datagen.mixed_chunks(max_size, n, seed)
+    sizes = [0, 1, 2, 3, 4, 5, 11, 12, 13, 14, 31, 32, 33, 63, 64, 65, 255, 256, 257, 1021] + list(
+        rng.integers(1, max_size + 1, n))
+    return [c[: int(s)] for c, s in zip(base, sizes[:n])]
+
+
+# ------------------------------------------------------------------ LZ4
+@pytest.mark.parametrize("tsize,type_id", [(1, 0), (1, 0xFF), (2, 3), (4, 4)])
+@pytest.mark.parametrize("max_chunk", [4096, 65536])
+def test_lz4_bit_exact_with_oracle(tsize, type_id, max_chunk):
+    g = _g()
+    chunks = [c[: len(c) // tsize * tsize] for c in ragged_chunks(max_chunk, 48, 1000 + max_chunk + tsize)]
+    chunks += datagen.mixed_chunks(max_chunk, 12, 77)
+    comp, dec, status, sizes, actual = g.roundtrip("lz4", chunks, opts=g.L.LZ4Opts(type_id), max_chunk=max_chunk)
+    for i, c in enumerate(chunks):
+        exp = o.lz4_compress(c, tsize, max_chunk)
+        assert comp[i].tobytes() == exp.tobytes(), f"chunk {i} (len {len(c)}) compressed stream differs"
+        assert status[i] == 0 and sizes[i] == len(c) and actual[i] == len(c)
+        assert dec[i].tobytes() == c.tobytes()
+
+
+def test_lz4_decodes_liblz4_streams():
+    g = _g()
+    from test_oracle_lz4 import stock_compress
+
+    chunks = ragged_chunks(65536, 40, 5)
+    comp = [stock_compress(c) for c in chunks]
+    out, actual, status = g.decode_raw("lz4", comp, [len(c) for c in chunks])
+    assert (status.cpu().numpy() == 0).all()
+    for d, c in zip(out.to_host(actual), chunks):
+        assert d.tobytes() == c.tobytes()
+
+
+def test_lz4_large_chunk_and_null_outputs():
+    g = _g()
+    chunks = [datagen.log_lines(1 << 20, 3), datagen.zipf_text(300000, 4), np.zeros(1 << 20, np.uint8)]
+    comp, dec, status, sizes, actual = g.roundtrip("lz4", chunks, max_chunk=1 << 20)
+    for i, c in enumerate(chunks):
+        assert comp[i].tobytes() == o.lz4_compress(c, 1, 1 << 20).tobytes()
+        assert dec[i].tobytes() == c.tobytes() and status[i] == 0
+    # NULL actual_bytes / statuses are allowed (reference SUPPORT_NULLPTR_APIS)
+    out, actual, status = g.decode_raw("lz4", comp, [len(c) for c in chunks], want_actual=False, want_status=False)
+    assert actual is None and status is None
+    for d, c in zip(out.to_host([len(c) for c in chunks]), chunks):
+        assert d.tobytes() == c.tobytes()
+
+
+def test_lz4_corrupt_input_matches_oracle_and_never_faults():
+    g = _g()
+    rng = np.random.default_rng(0)
+    junk = [(rng.integers(0, 4, int(n)) + 300).astype(np.int32).view(np.uint8) for n in rng.integers(25, 250, 64)]
+    junk += [rng.integers(0, 256, int(n), dtype=np.uint8) for n in rng.integers(1, 2000, 64)]
+    compb = g.B.DeviceBatch.from_host(junk)
+    sizes = g.B.decompress_sizes("lz4", compb).cpu().numpy()
+    caps = []
+    for s, j in zip(sizes, junk):
+        st, n = o.lz4_decompress(j, 0, write_output=False)
+        assert s == (n if st == 0 else 0)
+        caps.append(len(j) if (s == 0 or s > len(j)) else int(s) - 1)
+    out, actual, status = g.decode_raw("lz4", junk, caps)
+    st = status.cpu().numpy()
+    for i, (j, cap) in enumerate(zip(junk, caps)):
+        est, eout = o.lz4_decompress(j, cap)
+        assert st[i] == est
+        assert actual.cpu().numpy()[i] == len(eout)
+    assert (st == 12).all()  # the reference test requires every chunk to be flagged
+    # good stream into a too-small buffer
+    good = o.lz4_compress(datagen.log_lines(5000, 1))
+    _, actual, status = g.decode_raw("lz4", [good, good], [4999, 5000])
+    assert status.cpu().tolist() == [12, 0] and actual.cpu().tolist() == [0, 5000]
+
+
+# ------------------------------------------------------------------ Snappy
+@pytest.mark.parametrize("max_chunk", [4096, 65536])
+def test_snappy_bit_exact_with_oracle(max_chunk):
+    g = _g()
+    chunks = ragged_chunks(max_chunk, 48, 2000 + max_chunk) + datagen.mixed_chunks(max_chunk, 12, 78)
+    comp, dec, status, sizes, actual = g.roundtrip("snappy", chunks, max_chunk=max_chunk)
+    for i, c in enumerate(chunks):
+        exp = o.snappy_compress(c)
+        assert comp[i].tobytes() == exp.tobytes(), f"chunk {i} (len {len(c)}) compressed stream differs"
+        assert sizes[i] == len(c)
+        if len(c):
+            assert status[i] == 0 and actual[i] == len(c) and dec[i].tobytes() == c.tobytes()
+
+
+def test_snappy_reference_golden_and_unusual_streams():
+    g = _g()
+    import os
+
+    from test_oracle_snappy import GOLD, copy_elem, lit_header, varint
+
+    comp, raw = [], []
+    for i in (1, 2):
+        comp.append(np.frombuffer(open(os.path.join(GOLD, f"snappy_app_{i}.comp"), "rb").read(), np.uint8))
+        raw.append(open(os.path.join(GOLD, f"snappy_app_{i}.raw"), "rb").read())
+    big = bytes(i % 256 for i in range(512))
+    comp.append(np.frombuffer(varint(512) + lit_header(512) + big, np.uint8))
+    raw.append(big)
+    for n in ((1 << 15) + 100, (1 << 16) + 100):
+        head = np.random.default_rng(42).integers(0, 256, n, dtype=np.uint8).tobytes()
+        comp.append(np.frombuffer(varint(n + 35) + lit_header(n) + head + copy_elem(n, 35), np.uint8))
+        raw.append(head + head[:35])
+    out, actual, status = g.decode_raw("snappy", comp, [len(r) for r in raw])
+    assert (status.cpu().numpy() == 0).all()
+    for d, r in zip(out.to_host(actual), raw):
+        assert d.tobytes() == r
+
+
+def test_snappy_decodes_stock_streams_and_errors():
+    g = _g()
+    import pyarrow as pa
+
+    codec = pa.Codec("snappy")
+    chunks = [c for c in ragged_chunks(65536, 40, 6) if len(c)]
+    comp = [np.frombuffer(codec.compress(c.tobytes()).to_pybytes(), np.uint8) for c in chunks]
+    out, actual, status = g.decode_raw("snappy", comp, [len(c) for c in chunks])
+    assert (status.cpu().numpy() == 0).all()
+    for d, c in zip(out.to_host(actual), chunks):
+        assert d.tobytes() == c.tobytes()
+    # truncated / undersized: status and partial progress equal the oracle's
+    good = o.snappy_compress(datagen.zipf_text(5000, 3))
+    cases = [(good[:cut], 5000) for cut in range(1, len(good), 211)] + [(good, 4999), (good, 5000)]
+    out, actual, status = g.decode_raw("snappy", [c for c, _ in cases], [cap for _, cap in cases])
+    for i, (c, cap) in enumerate(cases):
+        est, eout = o.snappy_decompress(c, cap)
+        assert status.cpu().numpy()[i] == est and actual.cpu().numpy()[i] == len(eout)
+
+
+# ------------------------------------------------------------------ Cascaded
+@pytest.mark.parametrize("type_id", sorted(DTYPES))
+@pytest.mark.parametrize("opts", [(2, 1, 1), (1, 1, 1), (2, 1, 0), (0, 0, 1), (1, 0, 0), (0, 1, 0), (0, 0, 0), (2, 2, 1),
+                                  (3, 1, 1), (1, 2, 1), (7, 0, 1)])
+def test_cascaded_bit_exact_with_oracle(type_id, opts):
+    g = _g()
+    dt = DTYPES[type_id]
+    w = np.dtype(dt).itemsize
+    rng = np.random.default_rng(type_id * 100 + sum(opts))
+    parts = []
+    for n in (1, 2, 3, 31, 32, 33, 100, 4096 // w - 1, 4096 // w, 4096 // w + 1, 3 * 4096 // w + 17, 20000):
+        parts.append(datagen.sorted_ints(n, int(rng.integers(1 << 30))).astype(dt))
+    parts.append(np.zeros(5000, dt))                                     # one run per chunk
+    parts.append(rng.integers(0, 256, 6000 * w, dtype=np.uint8).view(dt))  # incompressible -> raw fallback
+    parts.append(np.repeat(np.array([3, 9, 4, 0, 1]), [1, 20, 13, 25, 6]).astype(dt))  # reference KAT input
+    parts.append((np.arange(3000) * 7 - 5000).astype(dt))                # negative values, constant delta
+    chunks = [p.view(np.uint8) for p in parts]
+    co = g.L.CascadedOpts(4096, type_id, *opts)
+    comp, dec, status, sizes, actual = g.roundtrip("cascaded", chunks, opts=co)
+    for i, c in enumerate(chunks):
+        exp = o.casc_compress(c, type_id, *opts)
+        assert comp[i].tobytes() == exp.tobytes(), f"partition {i} ({len(c)} B) compressed bytes differ from oracle"
+        assert sizes[i] == len(c) and status[i] == 0 and actual[i] == len(c)
+        assert dec[i].tobytes() == c.tobytes()
+
+
+def test_cascaded_reference_kat_words():
+    """tests/test_cascaded_batch.cpp:336-378 through the C ABI (int32, RLE=2, delta=1, no bit-packing)."""
+    g = _g()
+    x = np.repeat(np.array([3, 9, 4, 0, 1], np.int32), [1, 20, 13, 25, 6])
+    comp, *_ = g.roundtrip("cascaded", [x.view(np.uint8)], opts=g.L.CascadedOpts(4096, 4, 2, 1, 0))
+    w = comp[0].view(np.uint32)
+    assert w[0] == 2 + (1 << 8) + (4 << 24) and w[1] == x.nbytes
+    assert list(w[3:6]) == [10, 8, 16] and w[6].view(np.int32) == 3
+    assert list(comp[0][28:38].view(np.uint16)) == [1, 20, 13, 25, 6]
+    assert list(comp[0][40:48].view(np.uint16)) == [1, 1, 1, 1]
+    assert list(comp[0][48:64].view(np.int32)) == [6, -5, -4, 1]
+
+
+def test_cascaded_oob_matrix_and_size_query():
+    g = _g()
+    x = np.repeat(np.arange(3000, dtype=np.int32), 5).view(np.uint8)
+    comp = o.casc_compress(x, 4, 2, 1, 1)
+    cb, ub = len(comp), len(x)
+    cases = [(comp[: cb // 2 // 4 * 4], ub, 12), (comp, ub // 2, 12), (comp, ub - 1, 12), (comp, ub, 0)]
+    out, actual, status = g.decode_raw("cascaded", [c for c, _, _ in cases], [cap for _, cap, _ in cases])
+    assert status.cpu().tolist() == [e for _, _, e in cases]
+    assert actual.cpu().tolist() == [0, 0, 0, ub]
+    # truncations: same verdict as the oracle, never a fault
+    cuts = [comp[:k] for k in range(8, cb, 52)]
+    out, actual, status = g.decode_raw("cascaded", cuts, [ub] * len(cuts))
+    for i, c in enumerate(cuts):
+        est, _ = o.casc_decompress(c, ub, 4)
+        assert status.cpu().numpy()[i] == est
+    short = g.B.DeviceBatch.from_host([comp[:4], comp])
+    assert g.B.decompress_sizes("cascaded", short).cpu().tolist() == [0, ub]
+
+
+# ------------------------------------------------------------------ properties at scale
+@pytest.mark.parametrize("codec", ["lz4", "snappy"])
+def test_roundtrip_property_many_chunks(codec):
+    g = _g()
+    raw = np.concatenate([datagen.log_lines(8 << 20, 21), datagen.zipf_text(8 << 20, 22)])
+    chunks = [raw[i : i + 65536] for i in range(0, len(raw), 65536)]
+    comp, dec, status, sizes, actual = g.roundtrip(codec, chunks, max_chunk=65536)
+    assert (status == 0).all() and (actual == 65536).all() and (sizes == 65536).all()
+    assert np.concatenate(dec).tobytes() == raw.tobytes()
+    ratio = len(raw) / sum(len(c) for c in comp)
+    assert ratio > 1.5
