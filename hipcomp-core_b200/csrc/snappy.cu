@@ -202,6 +202,7 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const 
       const size_t cap = cap64 == 0 ? size : cap64; // 0 = "trust the preamble" (decompression.hiph:148-149)
       if ((cur >= comp_len && size != 0) || size > cap) ok = false;
     }
+    if (!ok) size = 0; // nothing was produced: report 0 bytes
     if (ok) {
       left = size;
       uint32_t dst = 0;
