@@ -34,7 +34,9 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "refgpu"],
+                    help="b200: this library; reference: the CPU codecs on the host cores; refgpu: the reference's "
+                         "own GPU build (oracle/_ref/libhipcomp_ref.so) through the same ABI, for context")
     ap.add_argument("--codec", default="lz4", choices=["lz4", "snappy", "cascaded"])
     ap.add_argument("--size-mib", type=int, default=None, help="uncompressed MiB per GPU (default: the BASELINE config)")
     ap.add_argument("--chunk", type=int, default=None)
@@ -286,6 +288,8 @@ class Plan:
         self.comp_sizes = torch.zeros(self.n, dtype=torch.int64, device=dev)
         self.temp_bytes = B.compress_temp_bytes(codec, self.n, chunk, self.opts)
         self.temp = torch.empty(max(self.temp_bytes, 16), dtype=torch.uint8, device=dev)
+        self.dtemp_bytes = B.decompress_temp_bytes(codec, self.n, chunk)
+        self.dtemp = torch.empty(max(self.dtemp_bytes, 16), dtype=torch.uint8, device=dev)
         self.back = torch.empty_like(raw)
         self.dst = B.DeviceBatch(self.back, off, np.full(self.n, chunk, np.int64))
         self.actual = torch.zeros(self.n, dtype=torch.int64, device=dev)
@@ -294,9 +298,10 @@ class Plan:
         lib = L.lib()
         self.f_comp = getattr(lib, f"hipcompBatched{name}CompressAsync")
         self.f_dec = getattr(lib, f"hipcompBatched{name}DecompressAsync")
-        self.f_gather = lib.b200compGatherChunksAsync
-        self.f_gather.restype = C.c_int
-        self.f_gather.argtypes = [C.c_void_p] * 4 + [C.c_size_t, C.c_void_p]
+        if hasattr(lib, "b200compGatherChunksAsync"):
+            self.f_gather = lib.b200compGatherChunksAsync
+            self.f_gather.restype = C.c_int
+            self.f_gather.argtypes = [C.c_void_p] * 4 + [C.c_size_t, C.c_void_p]
 
     def compress(self, src_ptrs=None, stream=None):
         s = C.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
@@ -309,7 +314,8 @@ class Plan:
         s = C.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
         st = self.f_dec(comp_ptrs if comp_ptrs is not None else self.comp.ptrs.data_ptr(),
                         (comp_sizes if comp_sizes is not None else self.comp_sizes).data_ptr(),
-                        self.dst.sizes.data_ptr(), self.actual.data_ptr(), self.n, None, 0, self.dst.ptrs.data_ptr(),
+                        self.dst.sizes.data_ptr(), self.actual.data_ptr(), self.n, self.dtemp.data_ptr(), self.dtemp_bytes,
+                        self.dst.ptrs.data_ptr(),
                         self.status.data_ptr(), s)
         assert st == 0, f"DecompressAsync -> {st}"
 
@@ -384,6 +390,7 @@ def run_b200(args):
     dominant = "compress" if t_comp >= t_dec else "decompress"
     ach = (alg_comp / (t_comp / K) if dominant == "compress" else alg_dec / (t_dec / K)) / GB
     line = {
+        **({"impl": "refgpu"} if args.impl == "refgpu" else {}),
         "metric": f"{args.codec}_roundtrip_throughput",
         "value": total_bytes * K / t_total_max / GB,
         "unit": "GB/s",
@@ -537,4 +544,8 @@ if __name__ == "__main__":
     if a.impl == "reference":
         run_reference(a)
     else:
+        if a.impl == "refgpu":
+            L = importlib.import_module("hipcomp-core_b200._lib")
+            L.use(L.load_from(os.path.join(ROOT, "oracle", "_ref", "libhipcomp_ref.so")))
+            a.no_e2e = True
         run_b200(a)

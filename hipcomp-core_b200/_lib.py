@@ -49,6 +49,23 @@ for _c, _opts in (("LZ4", LZ4Opts), ("Snappy", SnappyOpts), ("Cascaded", Cascade
 _lib = None
 
 
+def load_from(path):
+    """Bind the same 18 prototypes on another build of the same ABI (tests and bench.py use this
+    to drive the reference's own GPU library, oracle/_ref/libhipcomp_ref.so, as an oracle)."""
+    other = C.CDLL(path)
+    for name, args in PROTOTYPES.items():
+        fn = getattr(other, name)
+        fn.restype = C.c_int
+        fn.argtypes = args
+    return other
+
+
+def use(handle):
+    """Route this module's lib() to `handle` (None restores the product library)."""
+    global _lib
+    _lib = handle
+
+
 def lib():
     global _lib
     if _lib is None:

@@ -1,0 +1,121 @@
+"""-m gpu: the CUDA path vs the REFERENCE'S OWN GPU build (oracle/_ref/libhipcomp_ref.so, compiled
+from /root/reference by oracle/build_ref.sh) through the identical C ABI on identical inputs.
+
+  LZ4 / Snappy : compressed streams byte-identical; each side decodes the other's streams.
+  Cascaded     : compressed sizes identical, every defined byte identical (the reference leaves
+                 alignment padding and the FOR/width of empty bit-packed arrays uninitialised:
+                 those bytes are excluded with the oracle's layout map), cross-decoding both ways.
+Skipped when the reference build is absent.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import datagen
+import oracle_lib as o
+
+pytestmark = pytest.mark.gpu
+REF_SO = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libhipcomp_ref.so")
+
+
+@pytest.fixture(scope="module")
+def libs():
+    if not os.path.exists(REF_SO):
+        pytest.skip("oracle/_ref/libhipcomp_ref.so not built")
+    import gpu_common as g
+
+    ours = g.L.lib()
+    ref = g.L.load_from(REF_SO)
+    yield g, ours, ref
+    g.L.use(ours)
+
+
+def run_with(g, handle, fn):
+    g.L.use(handle)
+    try:
+        return fn()
+    finally:
+        g.L.use(None)
+        g.L.lib()
+
+
+def chunks_for(max_chunk, seed):
+    rng = np.random.default_rng(seed)
+    base = datagen.mixed_chunks(max_chunk, 36, seed)
+    sizes = [1, 5, 13, 14, 33, 64, 255, 1021] + list(rng.integers(1, max_chunk + 1, 28))
+    return [c[: int(s)] for c, s in zip(base, sizes)] + datagen.mixed_chunks(max_chunk, 12, seed + 1)
+
+
+@pytest.mark.parametrize("codec,max_chunk,type_id", [("lz4", 65536, 0), ("lz4", 4096, 0), ("lz4", 65536, 3), ("lz4", 65536, 4),
+                                                     ("snappy", 65536, 0), ("snappy", 4096, 0)])
+def test_lz_streams_identical_to_reference_gpu(libs, codec, max_chunk, type_id):
+    g, ours, ref = libs
+    w = {0: 1, 3: 2, 4: 4}[type_id]
+    chunks = [c[: len(c) // w * w] for c in chunks_for(max_chunk, 31 + max_chunk + type_id)]
+    chunks = [c for c in chunks if len(c)]
+    opts = g.L.LZ4Opts(type_id) if codec == "lz4" else None
+    a = run_with(g, ours, lambda: g.roundtrip(codec, chunks, opts=opts, max_chunk=max_chunk))
+    b = run_with(g, ref, lambda: g.roundtrip(codec, chunks, opts=opts, max_chunk=max_chunk))
+    for i, c in enumerate(chunks):
+        assert a[0][i].tobytes() == b[0][i].tobytes(), f"chunk {i} (len {len(c)}): stream differs from the reference GPU encoder"
+        assert b[1][i].tobytes() == c.tobytes() and a[1][i].tobytes() == c.tobytes()
+    # cross decode: reference decoder on our streams, our decoder on the reference's
+    caps = [len(c) for c in chunks]
+    out, actual, status = run_with(g, ref, lambda: g.decode_raw(codec, a[0], caps))
+    assert (status.cpu().numpy() == 0).all()
+    assert [d.tobytes() for d in out.to_host(actual)] == [c.tobytes() for c in chunks]
+    out, actual, status = run_with(g, ours, lambda: g.decode_raw(codec, b[0], caps))
+    assert (status.cpu().numpy() == 0).all()
+    assert [d.tobytes() for d in out.to_host(actual)] == [c.tobytes() for c in chunks]
+
+
+DTYPES = {0: np.int8, 1: np.uint8, 2: np.int16, 3: np.uint16, 4: np.int32, 5: np.uint32, 6: np.int64, 7: np.uint64}
+
+
+@pytest.mark.parametrize("type_id", sorted(DTYPES))
+@pytest.mark.parametrize("opts", [(2, 1, 1), (1, 1, 1), (2, 1, 0), (0, 0, 1), (1, 0, 1), (0, 1, 1), (0, 0, 0), (2, 2, 1)])
+def test_cascaded_identical_to_reference_gpu(libs, type_id, opts):
+    g, ours, ref = libs
+    dt = DTYPES[type_id]
+    w = np.dtype(dt).itemsize
+    rng = np.random.default_rng(type_id * 10 + sum(opts))
+    parts = [datagen.sorted_ints(n, int(rng.integers(1 << 30))).astype(dt)
+             for n in (1, 2, 33, 4096 // w, 4096 // w + 1, 3 * 4096 // w + 17, 20000)]
+    parts.append(rng.integers(0, 256, 6000 * w, dtype=np.uint8).view(dt))
+    parts.append((np.arange(3000) * 7 - 5000).astype(dt))
+    chunks = [p.view(np.uint8) for p in parts]
+    co = g.L.CascadedOpts(4096, type_id, *opts)
+
+    def comp_zeroed():
+        # zero the output first so bytes the reference never writes compare as 0
+        src = g.B.DeviceBatch.from_host(chunks)
+        stride = (max(len(c) for c in chunks) + 8 + 15) // 16 * 16 + 16
+        out = g.B.DeviceBatch.empty(src.n, stride)
+        out.buf.zero_()
+        comp = g.B.compress("cascaded", src, opts=co, out=out)
+        torch.cuda.synchronize()
+        return comp.to_host()
+
+    a = run_with(g, ours, comp_zeroed)
+    b = run_with(g, ref, comp_zeroed)
+    n_diff = 0
+    for i, c in enumerate(chunks):
+        assert len(a[i]) == len(b[i]), f"partition {i}: compressed size {len(a[i])} vs reference {len(b[i])}"
+        assert a[i][:8].tobytes() == b[i][:8].tobytes()
+        n_diff += int((a[i] != b[i]).sum())
+        exp = o.casc_compress(c, type_id, *opts)
+        assert a[i].tobytes() == exp.tobytes()
+    caps = [len(c) for c in chunks]
+    out, actual, status = run_with(g, ref, lambda: g.decode_raw("cascaded", a, caps))
+    assert (status.cpu().numpy() == 0).all(), "reference decoder rejected our stream"
+    assert [d.tobytes() for d in out.to_host(actual)] == [c.tobytes() for c in chunks]
+    out, actual, status = run_with(g, ours, lambda: g.decode_raw("cascaded", b, caps))
+    assert (status.cpu().numpy() == 0).all(), "our decoder rejected the reference stream"
+    assert [d.tobytes() for d in out.to_host(actual)] == [c.tobytes() for c in chunks]
+    # every differing byte must be a don't-care byte (padding / empty-array header): bounded, and
+    # neither decoder may depend on it (checked by the cross decodes above)
+    total = sum(len(x) for x in a)
+    assert n_diff <= total // 50, f"{n_diff} of {total} bytes differ from the reference"
+    print(f"type {type_id} opts {opts}: {n_diff} of {total} bytes differ (don't-care bytes)")
