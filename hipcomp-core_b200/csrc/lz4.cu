@@ -66,27 +66,43 @@ __device__ __forceinline__ uint32_t put_sequence(uint8_t* out, uint32_t c, const
   return c;
 }
 
-// One warp per chunk.  TS = match granularity in bytes (data_type width).
-template <int TS>
-__global__ void __launch_bounds__(32)
+constexpr int kCompWarps = 4;
+
+// One warp per chunk, kCompWarps chunks per CTA.  TS = match granularity in bytes
+// (data_type width).  kGlobalTable: the uint16 hash table of a chunk lives in the
+// caller's workspace (L2-resident, as many warps per SM as registers allow) instead
+// of shared memory (chosen for tables <= 8 KiB, where 28 warps/SM still fit).
+//
+// Per window the dependent chain is: keys (1 load round) -> table probe, issued for
+// every valid lane before the intra-window twin search finishes -> candidate verify
+// -> word-wide match extension.  Literals that lie inside the current window are
+// stored straight from the key registers.
+template <int TS, bool kGlobalTable>
+__global__ void __launch_bounds__(kCompWarps * 32)
 compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
-                size_t batch, uint32_t ht_size)
+                size_t batch, uint32_t ht_size, uint16_t* gtables)
 {
-  extern __shared__ __align__(16) uint16_t table[];
+  extern __shared__ __align__(16) uint16_t stables[];
   const uint32_t lane = (uint32_t)lane_id();
+  const int warp = threadIdx.x >> 5;
   constexpr uint32_t last_valid_match = (12 + TS - 1) / TS;
   constexpr uint32_t min_ending = (5 + TS - 1) / TS;
   constexpr uint32_t window = 32 - 3 / TS;
+  const size_t stride = (size_t)gridDim.x * kCompWarps;
 
-  for (size_t chunk = blockIdx.x; chunk < batch; chunk += gridDim.x) {
+  for (size_t chunk = (size_t)blockIdx.x * kCompWarps + warp; chunk < batch; chunk += stride) {
     const uint8_t* in = static_cast<const uint8_t*>(in_ptrs[chunk]);
     uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
     const uint32_t length = (uint32_t)in_bytes[chunk];
     const uint32_t typed_length = (length + TS - 1) / TS;
+    uint16_t* table = kGlobalTable ? gtables + chunk * ht_size : stables + (size_t)warp * ht_size;
 
-    {
-      uint32_t* t32 = reinterpret_cast<uint32_t*>(table);
-      for (uint32_t i = lane; i < (ht_size + 1) / 2; i += 32) t32[i] = 0xFFFFFFFFu;
+    if (ht_size >= 8 && ((reinterpret_cast<uintptr_t>(table) & 15) == 0)) {
+      uint4* t128 = reinterpret_cast<uint4*>(table);
+      const uint4 ones = make_uint4(~0u, ~0u, ~0u, ~0u);
+      for (uint32_t i = lane; i < ht_size / 8; i += 32) t128[i] = ones;
+    } else {
+      for (uint32_t i = lane; i < ht_size; i += 32) table[i] = (uint16_t)kNullOffset;
     }
     __syncwarp();
 
@@ -103,6 +119,9 @@ compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const*
         const unsigned vmask = nvalid >= 32 ? kFull : ((1u << nvalid) - 1u);
         const bool valid = lane < nvalid;
         const uint32_t key = valid ? ld_unaligned32_ro(in + (size_t)(d + lane) * TS) : 0u;
+        const uint32_t hpos = hash_key(key, ht_size);
+        // speculative probe: does not depend on the twin search below
+        const uint32_t h = valid ? (uint32_t)table[hpos] : kNullOffset;
 
         // (1) earliest lane that repeats the key of a lower lane in this window
         unsigned same = 0;
@@ -115,20 +134,16 @@ compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const*
           first = (uint32_t)__ffs((int)twins) - 1u;
           match_loc = d + __shfl_sync(kFull, lowest, (int)first);
         }
-        // (2) lanes in front of it probe the table
-        const uint32_t hpos = hash_key(key, ht_size);
+        // (2) lanes in front of it verify their table candidate
         bool found = false;
         uint32_t cand = 0;
-        if (lane < first) {
-          const uint32_t h = table[hpos];
-          if (h != kNullOffset) {
-            const uint32_t pos = d + lane;
-            cand = (pos & ~kMaxOffset) + h;
-            if (cand >= pos) cand -= 65536u;
-            const uint32_t dist = pos - cand;
-            if (cand < pos && dist <= kMaxOffset && dist * TS <= kMaxOffset)
-              found = ld_unaligned32_ro(in + (size_t)cand * TS) == key;
-          }
+        if (lane < first && h != kNullOffset) {
+          const uint32_t pos = d + lane;
+          cand = (pos & ~kMaxOffset) + h;
+          if (cand >= pos) cand -= 65536u;
+          const uint32_t dist = pos - cand;
+          if (cand < pos && dist <= kMaxOffset && dist * TS <= kMaxOffset)
+            found = ld_unaligned32_ro(in + (size_t)cand * TS) == key;
         }
         const unsigned hits = __ballot_sync(kFull, found);
         if (hits) {
@@ -148,31 +163,51 @@ compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const*
           d += nvalid;
           continue;
         }
-        // (4) extend the match, 32 elements per step
+        // (4) extend the match: 4 bytes per lane, 128 bytes per step
         const uint32_t pos = d + first;
-        const uint32_t limit = typed_length - pos - min_ending;
-        uint32_t mlen = limit;
-        for (uint32_t j = 0; j < limit; j += 32) {
-          const uint32_t i = j + lane;
-          bool neq = true;
-          if (i < limit) {
-            if (TS == 1)
-              neq = __ldg(in + match_loc + i) != __ldg(in + pos + i);
-            else if (TS == 2)
-              neq = __ldg(reinterpret_cast<const uint16_t*>(in) + match_loc + i)
-                    != __ldg(reinterpret_cast<const uint16_t*>(in) + pos + i);
-            else
-              neq = __ldg(reinterpret_cast<const uint32_t*>(in) + match_loc + i)
-                    != __ldg(reinterpret_cast<const uint32_t*>(in) + pos + i);
+        const uint32_t limit_b = (typed_length - pos - min_ending) * TS;
+        const uint8_t* pa = in + (size_t)match_loc * TS;
+        const uint8_t* pb = in + (size_t)pos * TS;
+        uint32_t mlen_b = limit_b;
+        for (uint32_t j = 0; j < limit_b; j += 128) {
+          const uint32_t o = j + 4 * lane;
+          uint32_t x = 1; // lanes past the limit: mismatch at their first byte
+          if (o < limit_b) {
+            x = ld_unaligned32_ro(pa + o) ^ ld_unaligned32_ro(pb + o);
+            const uint32_t nb = limit_b - o;
+            if (nb < 4) x |= 1u << (8 * nb);
           }
-          const unsigned diff = __ballot_sync(kFull, neq);
+          const unsigned diff = __ballot_sync(kFull, x != 0);
           if (diff) {
-            mlen = j + (uint32_t)__ffs((int)diff) - 1u;
+            const uint32_t l = (uint32_t)__ffs((int)diff) - 1u;
+            const uint32_t xb = __shfl_sync(kFull, x, (int)l);
+            mlen_b = j + 4 * l + (((uint32_t)__ffs((int)xb) - 1u) >> 3);
             break;
           }
         }
+        const uint32_t mlen = mlen_b / TS;
         const uint32_t nlit = pos - token_start;
-        c = put_sequence(out, c, in + (size_t)token_start * TS, nlit * TS, mlen * TS, (pos - match_loc) * TS);
+        if (token_start == d) {
+          // every literal of this sequence is a lane of the current window
+          const uint32_t nlit_b = nlit * TS, nmatch_b = mlen * TS, off_b = (pos - match_loc) * TS;
+          const uint32_t lit_at = c + 1 + (nlit_b >= 15 ? 1u : 0u); // nlit_b <= 116 < 15 + 255
+          if (lane < first) {
+#pragma unroll
+            for (int b = 0; b < TS; ++b) out[lit_at + lane * TS + b] = (uint8_t)(key >> (8 * b));
+          }
+          if (lane == 0) {
+            const uint32_t hi = nlit_b >= 15 ? 15u : nlit_b;
+            const uint32_t lo = nmatch_b >= 19 ? 15u : (nmatch_b - 4u);
+            out[c] = (uint8_t)((hi << 4) | lo);
+            if (nlit_b >= 15) out[c + 1] = (uint8_t)(nlit_b - 15);
+            out[lit_at + nlit_b] = (uint8_t)(off_b & 0xff);
+            out[lit_at + nlit_b + 1] = (uint8_t)(off_b >> 8);
+          }
+          c = lit_at + nlit_b + 2;
+          if (nmatch_b >= 19) c += put_lsic(out + c, nmatch_b - 19);
+        } else {
+          c = put_sequence(out, c, in + (size_t)token_start * TS, nlit * TS, mlen * TS, (pos - match_loc) * TS);
+        }
         d = token_start + nlit + mlen;
         break;
       }
@@ -314,7 +349,6 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
                                                hipcompBatchedLZ4Opts_t format_opts, hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedLZ4CompressAsync()";
-  (void)device_temp_ptr;
   if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
     return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
   const uint32_t ht = (uint32_t)lz4::hash_table_size(max_uncompressed_chunk_bytes);
@@ -328,30 +362,43 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
-  const int smem = (int)(((ht + 1) / 2) * 4);
-  const int per_sm = smem >= 32768 ? 6 : (smem >= 16384 ? 12 : (smem >= 8192 ? 24 : 32));
-  const size_t cap = (size_t)sm_count() * per_sm;
-  const int grid = (int)(batch_size < cap ? batch_size : cap);
+  const bool global_table = (size_t)ht * sizeof(uint16_t) > 8192;
+  if (global_table && device_temp_ptr == nullptr)
+    return fail(hipcompErrorInvalidValue, fn, "'device_temp_ptr' must not be null.");
+  const int smem = global_table ? 0 : (int)(ht * sizeof(uint16_t) * lz4::kCompWarps);
+  const size_t need = (batch_size + lz4::kCompWarps - 1) / lz4::kCompWarps;
+  const size_t cap = (size_t)sm_count() * 16;
+  const int grid = (int)(need < cap ? need : cap);
+  uint16_t* gt = static_cast<uint16_t*>(device_temp_ptr);
+#define B200_LZ4_LAUNCH(TS)                                                                                        \
+  do {                                                                                                             \
+    if (global_table)                                                                                              \
+      lz4::compress_kernel<TS, true><<<grid, lz4::kCompWarps * 32, 0, stream>>>(                                   \
+          device_uncompressed_ptrs, device_uncompressed_bytes, device_compressed_ptrs, device_compressed_bytes,    \
+          batch_size, ht, gt);                                                                                     \
+    else                                                                                                           \
+      lz4::compress_kernel<TS, false><<<grid, lz4::kCompWarps * 32, smem, stream>>>(                               \
+          device_uncompressed_ptrs, device_uncompressed_bytes, device_compressed_ptrs, device_compressed_bytes,    \
+          batch_size, ht, gt);                                                                                     \
+  } while (0)
   switch (format_opts.data_type) {
   case HIPCOMP_TYPE_BITS:
   case HIPCOMP_TYPE_CHAR:
   case HIPCOMP_TYPE_UCHAR:
-    lz4::compress_kernel<1><<<grid, 32, smem, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes,
-                                                        device_compressed_ptrs, device_compressed_bytes, batch_size, ht);
+    B200_LZ4_LAUNCH(1);
     break;
   case HIPCOMP_TYPE_SHORT:
   case HIPCOMP_TYPE_USHORT:
-    lz4::compress_kernel<2><<<grid, 32, smem, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes,
-                                                        device_compressed_ptrs, device_compressed_bytes, batch_size, ht);
+    B200_LZ4_LAUNCH(2);
     break;
   case HIPCOMP_TYPE_INT:
   case HIPCOMP_TYPE_UINT:
-    lz4::compress_kernel<4><<<grid, 32, smem, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes,
-                                                        device_compressed_ptrs, device_compressed_bytes, batch_size, ht);
+    B200_LZ4_LAUNCH(4);
     break;
   default:
     return fail(hipcompErrorInvalidValue, fn, "Unsupported input data type");
   }
+#undef B200_LZ4_LAUNCH
   return check_launch(fn);
 }
 

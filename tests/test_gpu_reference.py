@@ -75,14 +75,20 @@ DTYPES = {0: np.int8, 1: np.uint8, 2: np.int16, 3: np.uint16, 4: np.int32, 5: np
 
 
 @pytest.mark.parametrize("type_id", sorted(DTYPES))
-@pytest.mark.parametrize("opts", [(2, 1, 1), (1, 1, 1), (2, 1, 0), (0, 0, 1), (1, 0, 1), (0, 1, 1), (0, 0, 0), (2, 2, 1)])
+@pytest.mark.parametrize("opts", [(2, 1, 1), (1, 1, 1), (2, 1, 0), (0, 0, 1), (1, 0, 1), (0, 1, 1), (0, 0, 0), (3, 1, 1)])
 def test_cascaded_identical_to_reference_gpu(libs, type_id, opts):
     g, ours, ref = libs
     dt = DTYPES[type_id]
     w = np.dtype(dt).itemsize
     rng = np.random.default_rng(type_id * 10 + sum(opts))
-    parts = [datagen.sorted_ints(n, int(rng.integers(1 << 30))).astype(dt)
-             for n in (1, 2, 33, 4096 // w, 4096 // w + 1, 3 * 4096 // w + 17, 20000)]
+    # With >= 2 delta layers the reference build faults on B200 (unsigned underflow in
+    # block_delta_compress once an array collapses to 0 elements, SURVEY A.3 caveat 2, and its
+    # decode order is not an inverse for num_deltas > num_RLEs); those options are compared with
+    # the CPU oracle only (tests/test_gpu_parity.py).
+    sizes = (1, 2, 33, 4096 // w, 4096 // w + 1, 3 * 4096 // w + 17, 20000)
+    if opts[1] >= 2:
+        sizes = tuple(n for n in sizes if n >= 33)
+    parts = [datagen.sorted_ints(n, int(rng.integers(1 << 30))).astype(dt) for n in sizes]
     parts.append(rng.integers(0, 256, 6000 * w, dtype=np.uint8).view(dt))
     parts.append((np.arange(3000) * 7 - 5000).astype(dt))
     chunks = [p.view(np.uint8) for p in parts]
@@ -104,7 +110,11 @@ def test_cascaded_identical_to_reference_gpu(libs, type_id, opts):
     for i, c in enumerate(chunks):
         assert len(a[i]) == len(b[i]), f"partition {i}: compressed size {len(a[i])} vs reference {len(b[i])}"
         assert a[i][:8].tobytes() == b[i][:8].tobytes()
-        n_diff += int((a[i] != b[i]).sum())
+        differs = a[i] != b[i]
+        n_diff += int(differs.sum())
+        # we write 0 into every don't-care byte, the reference leaves garbage there: a differing
+        # byte that is non-zero on our side would be a real format difference
+        assert not a[i][differs].any(), f"partition {i}: a defined byte differs from the reference"
         exp = o.casc_compress(c, type_id, *opts)
         assert a[i].tobytes() == exp.tobytes()
     caps = [len(c) for c in chunks]
@@ -118,4 +128,5 @@ def test_cascaded_identical_to_reference_gpu(libs, type_id, opts):
     # neither decoder may depend on it (checked by the cross decodes above)
     total = sum(len(x) for x in a)
     assert n_diff <= total // 50, f"{n_diff} of {total} bytes differ from the reference"
-    print(f"type {type_id} opts {opts}: {n_diff} of {total} bytes differ (don't-care bytes)")
+    with open(os.path.join(os.path.dirname(REF_SO), "..", "..", "gpurun_out", "cascaded_vs_reference_diff.txt"), "a") as f:
+        f.write(f"type {type_id} opts {opts}: {n_diff} of {total} compressed bytes differ from the reference (don't-care bytes)\n")
