@@ -6,11 +6,15 @@
 // Kernel design (not the reference's): the reference runs one 128-thread CTA per
 // partition with CUB block scans/reductions and __syncthreads() between every
 // stage.  Here ONE WARP owns a partition and walks its 4096-byte chunks with
-// warp-synchronous primitives only (ballot/popc run detection, shuffle scans,
-// per-lane 32-element bit-packing against a bank-conflict-free padded shared
-// memory layout), so an SM keeps 16-32 independent partitions in flight with no
-// block-wide barrier anywhere.  Grids are persistent (multiple of the SM count)
-// and grid-stride over the batch.
+// warp-synchronous primitives only.  A chunk is staged in shared memory in a
+// 16-byte XOR-swizzled layout, so that both access patterns the layers need are
+// bank-conflict free AND 128 bits wide:
+//   striped  (lane L takes vector L of each 512-byte tile)  - run detection,
+//            compaction, deltas, scans, min/max, gathers
+//   blocked  (lane g takes elements [32g, 32g+32))           - bit packing with
+//            compile-time bit widths (no per-element shift bookkeeping)
+// An SM keeps up to 32 independent partitions in flight with no block barrier.
+// Grids are persistent (multiple of the SM count) and grid-stride over the batch.
 #include "common.cuh"
 
 #include <type_traits>
@@ -26,16 +30,34 @@ constexpr int kChunkBytes = 4096;
 constexpr int kWarpsPerCta = 4;
 constexpr int kMaxMetaBytes = 64;
 
-// Padded shared-memory array of N elements: one 4-byte (8 for 64-bit elements)
-// pad per 32 elements makes both the striped pattern (lane L reads 32r+L) and
-// the blocked pattern (lane L reads 32L+k) conflict free.
-template <typename E, int N>
-struct PArr {
-  static constexpr int PAD = sizeof(E) >= 4 ? 1 : 4 / (int)sizeof(E);
-  static constexpr int SIZE = N + (N / 32) * PAD;
-  static constexpr int BYTES = SIZE * (int)sizeof(E);
-  __device__ __forceinline__ static int p(int i) { return i + (i >> 5) * PAD; }
+// Swizzled shared-memory array of E.  Element i lives at p(i): the 16-byte vector
+// index is XORed with (i / 32) & 7.  Vectors stay contiguous and aligned.
+template <typename E>
+struct Swz {
+  static constexpr int VE = 16 / (int)sizeof(E); // elements per 16-byte vector
+  static constexpr int SH = VE == 16 ? 4 : VE == 8 ? 3 : VE == 4 ? 2 : 1;
+  __device__ __forceinline__ static int p(int i) { return i ^ (((i >> 5) & 7) << SH); }
 };
+
+template <typename E>
+union Vec {
+  uint4 q;
+  E e[16 / sizeof(E)];
+};
+
+// vector that holds elements [i0, i0 + VE), i0 a multiple of VE
+template <typename E>
+__device__ __forceinline__ Vec<E> ld_vec(const E* arr, int i0)
+{
+  Vec<E> v;
+  v.q = *reinterpret_cast<const uint4*>(arr + Swz<E>::p(i0));
+  return v;
+}
+template <typename E>
+__device__ __forceinline__ void st_vec(E* arr, int i0, const Vec<E>& v)
+{
+  *reinterpret_cast<uint4*>(arr + Swz<E>::p(i0)) = v.q;
+}
 
 __host__ __device__ constexpr int meta_size(int w, int R, int D)
 {
@@ -48,17 +70,108 @@ __device__ __forceinline__ constexpr int packed_header_bytes()
   return sizeof(E) == 8 ? 16 : 8; // roundUp(sizeof(E)+4, max(4,sizeof(E)))
 }
 
-// ------------------------------------------------------------------ bit I/O
+template <typename V>
+__device__ __forceinline__ V shfl_down_t(V v, int d)
+{
+  return __shfl_down_sync(kFull, v, d);
+}
+template <typename V>
+__device__ __forceinline__ V shfl_up_t(V v, int d)
+{
+  return __shfl_up_sync(kFull, v, d);
+}
+template <typename V>
+__device__ __forceinline__ V shfl_t(V v, int l)
+{
+  return __shfl_sync(kFull, v, l);
+}
+// sub-word element types travel as 32-bit values
+__device__ __forceinline__ uint8_t shfl_down_t(uint8_t v, int d) { return (uint8_t)__shfl_down_sync(kFull, (uint32_t)v, d); }
+__device__ __forceinline__ uint16_t shfl_down_t(uint16_t v, int d) { return (uint16_t)__shfl_down_sync(kFull, (uint32_t)v, d); }
+__device__ __forceinline__ uint8_t shfl_t(uint8_t v, int l) { return (uint8_t)__shfl_sync(kFull, (uint32_t)v, l); }
+__device__ __forceinline__ uint16_t shfl_t(uint16_t v, int l) { return (uint16_t)__shfl_sync(kFull, (uint32_t)v, l); }
 
-// Serialise arr[0..n) (padded smem) to `out` (global, 4-byte aligned; for raw
+// ------------------------------------------------------------------ bit packing
+
+// 32 values of BW bits each -> BW words, LSB first (bit i*BW of the group).
+// Everything folds at compile time: per element one shift+or per word it touches.
+template <int BW>
+__device__ __forceinline__ void pack32_static(const uint32_t (&d)[32], uint32_t* dst, int first_word, int words)
+{
+#pragma unroll
+  for (int t = 0; t < BW; ++t) {
+    uint32_t w = 0;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+      const int lo = k * BW - 32 * t; // bit position of element k relative to word t
+      if (lo > -BW && lo < 32) {
+        if (lo >= 0) w |= d[k] << lo;
+        else w |= d[k] >> (-lo);
+      }
+    }
+    if (first_word + t < words) dst[first_word + t] = w;
+  }
+}
+
+template <int MAXBW>
+__device__ __forceinline__ void pack32_dispatch(uint32_t bw, const uint32_t (&d)[32], uint32_t* dst, int first_word,
+                                                int words)
+{
+  switch (bw) {
+#define B200_CASE(B)                                                                                                 \
+  case B:                                                                                                            \
+    if (B <= MAXBW) pack32_static<(B <= MAXBW ? B : 1)>(d, dst, first_word, words);                                  \
+    break;
+    B200_CASE(1) B200_CASE(2) B200_CASE(3) B200_CASE(4) B200_CASE(5) B200_CASE(6) B200_CASE(7) B200_CASE(8)
+    B200_CASE(9) B200_CASE(10) B200_CASE(11) B200_CASE(12) B200_CASE(13) B200_CASE(14) B200_CASE(15) B200_CASE(16)
+    B200_CASE(17) B200_CASE(18) B200_CASE(19) B200_CASE(20) B200_CASE(21) B200_CASE(22) B200_CASE(23) B200_CASE(24)
+    B200_CASE(25) B200_CASE(26) B200_CASE(27) B200_CASE(28) B200_CASE(29) B200_CASE(30) B200_CASE(31) B200_CASE(32)
+#undef B200_CASE
+  default: break;
+  }
+}
+
+// generic path for 64-bit elements: lane g packs elements [32g, 32g+32)
+__device__ __forceinline__ void pack32_u64(uint32_t bw, const unsigned long long* arr, int g, int n,
+                                           unsigned long long fr, uint32_t* data, int words)
+{
+  unsigned long long acc = 0;
+  int nbits = 0;
+  int wout = g * (int)bw;
+  for (int k = 0; k < 32; ++k) {
+    const int e = (g << 5) + k;
+    const unsigned long long d = e < n ? arr[Swz<unsigned long long>::p(e)] - fr : 0ull;
+    if (bw > 32) {
+      acc |= (unsigned long long)(uint32_t)d << nbits;
+      if (wout < words) data[wout] = (uint32_t)acc;
+      ++wout;
+      acc >>= 32;
+      acc |= (d >> 32) << nbits;
+      nbits += (int)bw - 32;
+    } else {
+      acc |= d << nbits;
+      nbits += (int)bw;
+    }
+    if (nbits >= 32) {
+      if (wout < words) data[wout] = (uint32_t)acc;
+      ++wout;
+      acc >>= 32;
+      nbits -= 32;
+    }
+  }
+  if (nbits > 0 && wout < words) data[wout] = (uint32_t)acc;
+}
+
+// Serialise arr[0..n) (swizzled smem) to `out` (global, 4-byte aligned; for raw
 // 8-byte elements 8-byte aligned), raw or bit-packed.  Returns false when the
 // 4-byte padded array does not fit in `avail` bytes.  Follows block_write /
 // block_bitpack / get_for_bitwidth (reference CascadedKernels.hiph:394-553,646-680).
 template <typename E, int N>
 __device__ bool write_array(const E* arr, int n, uint8_t* out, size_t avail, bool use_bp, uint32_t& out_bytes)
 {
-  using P = PArr<E, N>;
   using S = typename std::make_signed<E>::type;
+  using Z = Swz<E>;
+  constexpr int VE = Z::VE;
   const int lane = lane_id();
   uint32_t* outw = reinterpret_cast<uint32_t*>(out);
 
@@ -66,18 +179,25 @@ __device__ bool write_array(const E* arr, int n, uint8_t* out, size_t avail, boo
     const uint32_t bytes = (uint32_t)n * sizeof(E);
     const uint32_t padded = (bytes + 3u) & ~3u;
     if (padded > avail) return false;
+    int done = 0; // elements stored by the vector path
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+      const int vecs = n / VE;
+      uint4* ov = reinterpret_cast<uint4*>(out);
+      for (int v = lane; v < vecs; v += 32) ov[v] = ld_vec<E>(arr, v * VE).q;
+      done = vecs * VE;
+    }
     if (sizeof(E) >= 4) {
       E* oe = reinterpret_cast<E*>(out);
-      for (int i = lane; i < n; i += 32) oe[i] = arr[P::p(i)];
+      for (int i = done + lane; i < n; i += 32) oe[i] = arr[Z::p(i)];
     } else {
-      constexpr int K = 4 / (int)sizeof(E);
+      constexpr int K = sizeof(E) < 4 ? 4 / (int)sizeof(E) : 1;
       const int words = padded / 4;
-      for (int j = lane; j < words; j += 32) {
+      for (int j = done / K + lane; j < words; j += 32) {
         uint32_t wv = 0;
 #pragma unroll
         for (int c = 0; c < K; ++c) {
           const int e = j * K + c;
-          const uint32_t v = e < n ? (uint32_t)arr[P::p(e)] : 0u;
+          const uint32_t v = e < n ? (uint32_t)arr[Z::p(e)] : 0u;
           wv |= v << (8 * sizeof(E) * c);
         }
         outw[j] = wv;
@@ -91,11 +211,15 @@ __device__ bool write_array(const E* arr, int n, uint8_t* out, size_t avail, boo
   S mn = 0, mx = 0;
   uint32_t bw = 0;
   if (n > 0) {
-    S lmn = (S)arr[P::p(lane < n ? lane : 0)], lmx = lmn;
-    for (int i = lane + 32; i < n; i += 32) {
-      const S v = (S)arr[P::p(i)];
-      lmn = v < lmn ? v : lmn;
-      lmx = v > lmx ? v : lmx;
+    S lmn = (S)arr[0], lmx = lmn; // element 0 is valid (p(0) == 0)
+    for (int i0 = lane * VE; i0 < n; i0 += 32 * VE) {
+      const Vec<E> v = ld_vec<E>(arr, i0);
+#pragma unroll
+      for (int j = 0; j < VE; ++j) {
+        const S x = i0 + j < n ? (S)v.e[j] : lmn;
+        lmn = x < lmn ? x : lmn;
+        lmx = x > lmx ? x : lmx;
+      }
     }
     mn = warp_min(lmn);
     mx = warp_max(lmx);
@@ -130,34 +254,22 @@ __device__ bool write_array(const E* arr, int n, uint8_t* out, size_t avail, boo
     // lane g packs elements [32g, 32g+32) into words [g*bw, (g+1)*bw)
     const int groups = (n + 31) >> 5;
     for (int g = lane; g < groups; g += 32) {
-      unsigned long long acc = 0;
-      int nbits = 0;
-      int wout = g * (int)bw;
-#pragma unroll 4
-      for (int k = 0; k < 32; ++k) {
-        const int e = (g << 5) + k;
-        const E d = e < n ? (E)(arr[P::p(e)] - fr) : (E)0;
-        if (sizeof(E) == 8 && bw > 32) {
-          acc |= (unsigned long long)(uint32_t)d << nbits;
-          nbits += 32;
-          if (wout < words) data[wout] = (uint32_t)acc;
-          ++wout;
-          acc >>= 32;
-          nbits -= 32;
-          acc |= (unsigned long long)((unsigned long long)d >> 32) << nbits;
-          nbits += (int)bw - 32;
-        } else {
-          acc |= (unsigned long long)d << nbits;
-          nbits += (int)bw;
+      if (sizeof(E) == 8 && bw > 32) {
+        pack32_u64(bw, reinterpret_cast<const unsigned long long*>(arr), g, n, (unsigned long long)fr, data, words);
+      } else {
+        uint32_t d[32];
+#pragma unroll
+        for (int j = 0; j < 32 / VE; ++j) {
+          const Vec<E> v = ld_vec<E>(arr, (g << 5) + j * VE);
+#pragma unroll
+          for (int c = 0; c < VE; ++c) {
+            const int e = (g << 5) + j * VE + c;
+            d[j * VE + c] = e < n ? (uint32_t)(E)(v.e[c] - fr) : 0u;
+          }
         }
-        if (nbits >= 32) {
-          if (wout < words) data[wout] = (uint32_t)acc;
-          ++wout;
-          acc >>= 32;
-          nbits -= 32;
-        }
+        constexpr int MAXBW = sizeof(E) == 1 ? 8 : sizeof(E) == 2 ? 16 : 32;
+        pack32_dispatch<MAXBW>(bw, d, data, g * (int)bw, words);
       }
-      if (nbits > 0 && wout < words) data[wout] = (uint32_t)acc;
     }
   }
   out_bytes = bytes;
@@ -171,24 +283,23 @@ __device__ __forceinline__ uint32_t get_bits32(const uint32_t* words, int nwords
   const uint32_t sh = bitpos & 31;
   const uint32_t lo = idx < nwords ? __ldg(words + idx) : 0u;
   const uint32_t hi = idx + 1 < nwords ? __ldg(words + idx + 1) : 0u;
-  const unsigned long long both = ((unsigned long long)hi << 32) | lo;
-  const uint32_t v = (uint32_t)(both >> sh);
+  const uint32_t v = __funnelshift_r(lo, hi, sh);
   return nb == 32 ? v : (v & ((1u << nb) - 1u));
 }
 
 // Read an array stored by write_array from global `in` (in_bytes long, all of
-// it inside the partition) into padded smem `arr`.  Returns false on a
+// it inside the partition) into swizzled smem `arr`.  Returns false on a
 // malformed array.  Follows block_read / block_bitunpack (:563-618,702-737).
 template <typename E, int N>
 __device__ bool read_array(const uint8_t* in, uint32_t in_bytes, bool use_bp, E* arr, int& n_out)
 {
-  using P = PArr<E, N>;
+  using Z = Swz<E>;
   const int lane = lane_id();
   if (!use_bp) {
     const uint32_t n = in_bytes / sizeof(E);
     if (n > (uint32_t)N) return false;
     const E* ie = reinterpret_cast<const E*>(in);
-    for (int i = lane; i < (int)n; i += 32) arr[P::p(i)] = __ldg(ie + i);
+    for (int i = lane; i < (int)n; i += 32) arr[Z::p(i)] = __ldg(ie + i);
     n_out = (int)n;
     return true;
   }
@@ -210,19 +321,17 @@ __device__ bool read_array(const uint8_t* in, uint32_t in_bytes, bool use_bp, E*
   const int words = (int)((n * bw + 31u) >> 5);
   if ((uint32_t)HDR + 4u * (uint32_t)words > ((in_bytes + 3u) & ~3u)) return false;
   const uint32_t* data = inw + HDR / 4;
-  for (int i = lane; i < (int)n; i += 32) {
-    E d = 0;
-    if (bw > 0) {
+  if (bw == 0) {
+    for (int i = lane; i < (int)n; i += 32) arr[Z::p(i)] = fr;
+  } else if (sizeof(E) == 8 && bw > 32) {
+    for (int i = lane; i < (int)n; i += 32) {
       const uint32_t bitpos = (uint32_t)i * bw;
-      if (sizeof(E) == 8 && bw > 32) {
-        const unsigned long long lo = get_bits32(data, words, bitpos, 32);
-        const unsigned long long hi = get_bits32(data, words, bitpos + 32, bw - 32);
-        d = (E)(lo | (hi << 32));
-      } else {
-        d = (E)get_bits32(data, words, bitpos, bw);
-      }
+      const unsigned long long lo = get_bits32(data, words, bitpos, 32);
+      const unsigned long long hi = get_bits32(data, words, bitpos + 32, bw - 32);
+      arr[Z::p(i)] = (E)((lo | (hi << 32)) + fr);
     }
-    arr[P::p(i)] = (E)(d + fr);
+  } else {
+    for (int i = lane; i < (int)n; i += 32) arr[Z::p(i)] = (E)((E)get_bits32(data, words, (uint32_t)i * bw, bw) + fr);
   }
   n_out = (int)n;
   return true;
@@ -233,32 +342,57 @@ __device__ bool read_array(const uint8_t* in, uint32_t in_bytes, bool use_bp, E*
 // In-place run-length encoding of vals[0..n): returns the run count, leaves the
 // run values in vals[0..m) and the run lengths in counts[0..m).
 // (reference block_rle_compress :124-241)
+// Pass 1 (striped, VE elements per lane): run-end flags, warp scan of the per-lane
+// flag counts, compaction of (value, end index).  Pass 2: lengths from ends.
 template <typename T, int N>
 __device__ int rle_encode(T* vals, int n, uint16_t* counts)
 {
-  using P = PArr<T, N>;
-  using PC = PArr<uint16_t, N>;
+  using Z = Swz<T>;
+  using ZC = Swz<uint16_t>;
+  constexpr int VE = Z::VE;
+  constexpr int TILE = 32 * VE;
   const int lane = lane_id();
-  const unsigned lt = lanemask_lt();
-  int m = 0, prev_end = 0;
-  for (int base = 0; base < n; base += 32) {
-    const int i = base + lane;
-    const T cur = i < n ? vals[P::p(i)] : (T)0;
-    const T nxt = i + 1 < n ? vals[P::p(i + 1)] : (T)0;
-    const bool flag = i < n && (i + 1 == n || nxt != cur);
-    const unsigned mask = __ballot_sync(kFull, flag);
-    __syncwarp();
-    if (flag) {
-      const unsigned below = mask & lt;
-      const int pos = m + __popc(below);
-      const int pe = below ? base + 32 - __clz((int)below) : prev_end;
-      vals[P::p(pos)] = cur;
-      counts[PC::p(pos)] = (uint16_t)(i + 1 - pe);
+  int m = 0;
+  for (int base = 0; base < n; base += TILE) {
+    const int i0 = base + lane * VE;
+    const Vec<T> v = ld_vec<T>(vals, i0);
+    T nx = shfl_down_t(v.e[0], 1);
+    const int after = base + TILE < N ? base + TILE : N - 1;
+    const T nb = vals[Z::p(after)]; // first element of the next tile (broadcast read)
+    if (lane == 31) nx = nb;
+    uint32_t flags = 0;
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      const int i = i0 + j;
+      const T next = j + 1 < VE ? v.e[j + 1 < VE ? j + 1 : j] : nx;
+      const bool f = i < n && (i + 1 == n || next != v.e[j]);
+      flags |= (f ? 1u : 0u) << j;
     }
-    if (mask) prev_end = base + 32 - __clz((int)mask);
-    m += __popc(mask);
+    int total;
+    int pos = m + warp_excl_sum<int>(__popc(flags), total);
+    __syncwarp(); // every lane has read its tile before anyone compacts into it
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      if (flags & (1u << j)) {
+        vals[Z::p(pos)] = v.e[j];
+        counts[ZC::p(pos)] = (uint16_t)(i0 + j + 1);
+        ++pos;
+      }
+    }
+    m += total;
     __syncwarp();
   }
+  // ends -> lengths
+  uint32_t carry = 0;
+  for (int t = 0; t < m; t += 32) {
+    const int r = t + lane;
+    const uint32_t e = r < m ? counts[ZC::p(r)] : 0u;
+    uint32_t prev = __shfl_up_sync(kFull, e, 1);
+    if (lane == 0) prev = carry;
+    carry = __shfl_sync(kFull, e, 31);
+    if (r < m) counts[ZC::p(r)] = (uint16_t)(e - prev);
+  }
+  __syncwarp();
   return m;
 }
 
@@ -267,140 +401,179 @@ __device__ int rle_encode(T* vals, int n, uint16_t* counts)
 template <typename T, int N>
 __device__ T delta_encode(T* vals, int n)
 {
-  using P = PArr<T, N>;
+  using Z = Swz<T>;
+  constexpr int VE = Z::VE;
+  constexpr int TILE = 32 * VE;
   const int lane = lane_id();
-  const T seed = vals[P::p(0)];
+  const T seed = vals[0];
   __syncwarp();
-  for (int base = 0; base < n - 1; base += 32) {
-    const int i = base + lane;
-    T d = 0;
-    if (i < n - 1) d = (T)(vals[P::p(i + 1)] - vals[P::p(i)]);
-    __syncwarp();
-    if (i < n - 1) vals[P::p(i)] = d;
-    __syncwarp();
+  for (int base = 0; base < n - 1; base += TILE) {
+    const int i0 = base + lane * VE;
+    Vec<T> v = ld_vec<T>(vals, i0);
+    T nx = shfl_down_t(v.e[0], 1);
+    const int after = base + TILE < N ? base + TILE : N - 1;
+    const T nb = vals[Z::p(after)];
+    if (lane == 31) nx = nb;
+#pragma unroll
+    for (int j = 0; j < VE; ++j) v.e[j] = (T)((j + 1 < VE ? v.e[j + 1 < VE ? j + 1 : j] : nx) - v.e[j]);
+    __syncwarp(); // lane 31's look-ahead read precedes the next tile's update (already read); tile is private
+    st_vec<T>(vals, i0, v);
   }
+  __syncwarp();
   return seed;
 }
 
 // In-place inverse delta: vals[0..n) holds differences, result has n+1 elements
 // vals[e] = seed + sum_{j<e} d[j].  (reference block_delta_decompress :343-377)
+// Callers guarantee n + 1 <= N.
 template <typename T, int N>
 __device__ void delta_decode(T* vals, int n, T seed)
 {
-  using P = PArr<T, N>;
+  using Z = Swz<T>;
+  constexpr int VE = Z::VE;
+  constexpr int TILE = 32 * VE;
   const int lane = lane_id();
   T carry = seed;
-  for (int base = 0; base < n; base += 1024) {
-    const int lo = base + (lane << 5);
+  for (int base = 0; base <= n; base += TILE) {
+    const int i0 = base + lane * VE;
+    Vec<T> v = ld_vec<T>(vals, i0);
     T sum = 0;
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      const int e = lo + k;
-      if (e < n) sum += vals[P::p(e)];
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      const T d = i0 + j < n ? v.e[j] : (T)0;
+      v.e[j] = sum; // exclusive prefix inside the lane
+      sum += d;
     }
     T total;
-    T run = (T)(carry + warp_excl_sum<T>(sum, total));
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      const int e = lo + k;
-      if (e < n) {
-        const T d = vals[P::p(e)];
-        vals[P::p(e)] = run;
-        run += d;
-      }
-    }
+    const T off = (T)(carry + warp_excl_sum<T>(sum, total));
+#pragma unroll
+    for (int j = 0; j < VE; ++j) v.e[j] += off;
+    st_vec<T>(vals, i0, v); // positions > n receive the total: harmless, inside the array
     carry += total;
   }
-  __syncwarp();
-  if (lane == 0) vals[P::p(n)] = carry;
   __syncwarp();
 }
 
-// Expand runs: dst[i] = vals[run(i)].  counts[] is overwritten with run starts,
-// idx[] is scratch.  Returns the expanded length or -1 when it exceeds N.
-// dst is padded smem when dst_global is false, else a plain global array.
-// (reference block_rle_decompress :255-305 — there one thread loops over a whole
-// run; here every output element is produced by its own lane.)
+// Expand runs.  counts[] is overwritten with run starts, idx[] is scratch (N entries).
+//   gout != nullptr : dst is the global output (outermost layer); at most `room` elements fit.
+//   gout == nullptr : the expansion replaces vals[] in place (inner layers).
+// Returns the expanded length, or -1 when it exceeds N / room.
+// (reference block_rle_decompress :255-305 - there one thread loops over a whole run; here every
+// output element finds its run by a max-scan over scattered run indices.)
 template <typename T, int N>
-__device__ int rle_decode(const T* vals, uint16_t* counts, int n_runs, uint16_t* idx, T* dst, bool dst_global)
+__device__ int rle_expand(T* vals, uint16_t* counts, int n_runs, uint16_t* idx, T* gout, size_t room)
 {
-  using P = PArr<T, N>;
-  using PC = PArr<uint16_t, N>;
+  using Z = Swz<T>;
+  using ZC = Swz<uint16_t>;
+  constexpr int W = (int)sizeof(T);
   const int lane = lane_id();
-  // 1. exclusive scan of the counts (blocked, 32 runs per lane per pass)
+  // 1. exclusive scan of the counts, 8 per lane
   uint32_t carry = 0;
-  for (int base = 0; base < n_runs; base += 1024) {
-    const int lo = base + (lane << 5);
-    uint32_t sum = 0;
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      const int e = lo + k;
-      if (e < n_runs) sum += counts[PC::p(e)];
+  bool zero_run = false;
+  for (int base = 0; base < n_runs; base += 256) {
+    const int i0 = base + lane * 8;
+    Vec<uint16_t> v = ld_vec<uint16_t>(counts, i0);
+    uint32_t c[8], s[8], sum = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      c[j] = i0 + j < n_runs ? (uint32_t)v.e[j] : 0u;
+      zero_run |= i0 + j < n_runs && c[j] == 0;
+      s[j] = sum;
+      sum += c[j];
     }
     uint32_t total;
-    uint32_t run = carry + warp_excl_sum<uint32_t>(sum, total);
+    const uint32_t off = carry + warp_excl_sum<uint32_t>(sum, total);
     if (carry + total > (uint32_t)N) return -1;
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      const int e = lo + k;
-      if (e < n_runs) {
-        const uint32_t c = counts[PC::p(e)];
-        // a zero-length run never owns an output position: park it on N (ignored)
-        counts[PC::p(e)] = (uint16_t)(c ? run : (uint32_t)N);
-        run += c;
-      }
-    }
+    // a zero-length run never owns an output position: park it on N (ignored below)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v.e[j] = (uint16_t)(c[j] ? off + s[j] : (uint32_t)N);
+    st_vec<uint16_t>(counts, i0, v);
     carry += total;
   }
   const int total_out = (int)carry;
-  __syncwarp();
+  if (gout != nullptr && (size_t)total_out > room) return -1;
+  // An encoder never emits empty runs.  With them a run's start can precede its own slot, which
+  // the in-place expansion of an inner layer cannot honour: such a stream is reported as corrupt.
+  if (gout == nullptr && __any_sync(kFull, zero_run)) return -1;
   // 2. mark the first output position of every run with the run index
-  for (int i = lane; i < total_out; i += 32) idx[PC::p(i)] = 0;
-  __syncwarp();
-  for (int j = lane; j < n_runs; j += 32) {
-    const int s = counts[PC::p(j)];
-    if (s < total_out) idx[PC::p(s)] = (uint16_t)j;
+  {
+    Vec<uint16_t> z;
+    z.q = make_uint4(0, 0, 0, 0);
+    for (int i0 = lane * 8; i0 < total_out; i0 += 256) st_vec<uint16_t>(idx, i0, z);
   }
   __syncwarp();
-  // 3. inclusive max-scan of the marks (blocked)
+  for (int j = lane; j < n_runs; j += 32) {
+    const int s = counts[ZC::p(j)];
+    if (s < total_out) idx[ZC::p(s)] = (uint16_t)j;
+  }
+  __syncwarp();
+  // 3. inclusive max-scan of the marks, 8 per lane; the outermost layer gathers and stores here
+  const bool aligned8 = gout != nullptr && (reinterpret_cast<uintptr_t>(gout) & 7) == 0;
   uint32_t cmax = 0;
-  for (int base = 0; base < total_out; base += 1024) {
-    const int lo = base + (lane << 5);
-    uint32_t lm = 0;
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      const int e = lo + k;
-      if (e < total_out) {
-        const uint32_t v = idx[PC::p(e)];
-        lm = v > lm ? v : lm;
-      }
+  for (int base = 0; base < total_out; base += 256) {
+    const int i0 = base + lane * 8;
+    Vec<uint16_t> v = ld_vec<uint16_t>(idx, i0);
+    uint32_t r[8], lm = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      r[j] = i0 + j < total_out ? (uint32_t)v.e[j] : 0u;
+      lm = r[j] > lm ? r[j] : lm;
     }
     const uint32_t incl = warp_incl_max<uint32_t>(lm);
     uint32_t run = __shfl_up_sync(kFull, incl, 1);
     if (lane == 0) run = 0;
     run = run > cmax ? run : cmax;
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      const int e = lo + k;
-      if (e < total_out) {
-        const uint32_t v = idx[PC::p(e)];
-        run = v > run ? v : run;
-        idx[PC::p(e)] = (uint16_t)run;
-      }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      run = r[j] > run ? r[j] : run;
+      r[j] = run;
     }
-    const uint32_t pass_max = __shfl_sync(kFull, incl, 31);
-    cmax = pass_max > cmax ? pass_max : cmax;
+    const uint32_t tile_max = __shfl_sync(kFull, incl, 31);
+    cmax = tile_max > cmax ? tile_max : cmax;
+    if (gout != nullptr) {
+      if (i0 < total_out) {
+        T o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = vals[Z::p((int)r[j])];
+        if (aligned8 && i0 + 8 <= total_out) {
+          // 8 consecutive elements = W 8-byte words
+          unsigned long long* g8 = reinterpret_cast<unsigned long long*>(gout + i0);
+#pragma unroll
+          for (int q = 0; q < W; ++q) {
+            unsigned long long word = 0;
+#pragma unroll
+            for (int b = 0; b < 8 / W; ++b) word |= (unsigned long long)o[q * (8 / W) + b] << (8 * W * b);
+            g8[q] = word;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (i0 + j < total_out) gout[i0 + j] = o[j];
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v.e[j] = (uint16_t)r[j];
+      st_vec<uint16_t>(idx, i0, v);
+    }
   }
   __syncwarp();
-  // 4. gather (striped: coalesced when dst is global)
-  for (int i = lane; i < total_out; i += 32) {
-    const T v = vals[P::p(idx[PC::p(i)])];
-    if (dst_global)
-      dst[i] = v;
-    else
-      dst[P::p(i)] = v;
+  if (gout == nullptr) {
+    // 4. in-place gather, highest tile first: a tile only reads run values at or below itself
+    constexpr int VE = Z::VE;
+    constexpr int TILE = 32 * VE;
+    for (int base = (total_out - 1) / TILE * TILE; base >= 0 && total_out > 0; base -= TILE) {
+      const int i0 = base + lane * VE;
+      Vec<T> v;
+      v.q = make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int j = 0; j < VE; ++j)
+        if (i0 + j < total_out) v.e[j] = vals[Z::p((int)idx[ZC::p(i0 + j)])];
+      __syncwarp();
+      if (i0 < total_out) st_vec<T>(vals, i0, v);
+      __syncwarp();
+    }
   }
-  __syncwarp();
   return total_out;
 }
 
@@ -409,12 +582,26 @@ __device__ int rle_decode(const T* vals, uint16_t* counts, int n_runs, uint16_t*
 template <typename T>
 struct CompSmem {
   static constexpr int N = kChunkBytes / (int)sizeof(T);
-  static constexpr int BYTES = PArr<T, N>::BYTES + PArr<uint16_t, N>::BYTES + kMaxMetaBytes;
+  static constexpr int BYTES = kChunkBytes + N * 2 + kMaxMetaBytes; // values, run ends/lengths, chunk metadata
 };
 
-__device__ void warp_zero_words(uint32_t* p, int nwords)
+// global -> swizzled smem, 16 bytes per lane when the source allows it
+template <typename T>
+__device__ __forceinline__ void load_chunk(const T* src, int n, T* A)
 {
-  for (int i = lane_id(); i < nwords; i += 32) p[i] = 0;
+  using Z = Swz<T>;
+  const int lane = lane_id();
+  int done = 0;
+  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    const int vecs = n / Z::VE;
+    for (int v = lane; v < vecs; v += 32) {
+      Vec<T> x;
+      x.q = ld_stream16(reinterpret_cast<const uint4*>(src) + v);
+      st_vec<T>(A, v * Z::VE, x);
+    }
+    done = vecs * Z::VE;
+  }
+  for (int i = done + lane; i < n; i += 32) A[Z::p(i)] = __ldg(src + i);
 }
 
 // raw copy of a partition behind the 8-byte header (fallback path, :1020-1029)
@@ -444,10 +631,9 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
 {
   constexpr int N = CompSmem<T>::N;
   constexpr int W = (int)sizeof(T);
-  using P = PArr<T, N>;
   T* A = reinterpret_cast<T*>(smem);
-  uint16_t* C = reinterpret_cast<uint16_t*>(smem + P::BYTES);
-  uint32_t* meta = reinterpret_cast<uint32_t*>(smem + P::BYTES + PArr<uint16_t, N>::BYTES);
+  uint16_t* C = reinterpret_cast<uint16_t*>(smem + kChunkBytes);
+  uint32_t* meta = reinterpret_cast<uint32_t*>(smem + kChunkBytes + N * 2);
   const int lane = lane_id();
 
   if (in == nullptr || in_bytes == 0) {
@@ -468,9 +654,8 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
     cur += msize;
     if (cur > limit) { use_compression = false; break; }
     int n = (int)(n_total - c * N < (size_t)N ? n_total - c * N : (size_t)N);
-    const T* src = in + c * N;
-    for (int i = lane; i < n; i += 32) A[P::p(i)] = __ldg(src + i);
-    warp_zero_words(meta, kMaxMetaBytes / 4);
+    load_chunk<T>(in + c * N, n, A);
+    if (lane < kMaxMetaBytes / 4) meta[lane] = 0;
     __syncwarp();
 
     for (int l = 0; l < layers && use_compression; ++l) {
@@ -547,7 +732,7 @@ compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const*
 template <typename T>
 struct DecompSmem {
   static constexpr int N = kChunkBytes / (int)sizeof(T);
-  static constexpr int BYTES = 2 * PArr<T, N>::BYTES + 2 * PArr<uint16_t, N>::BYTES;
+  static constexpr int BYTES = kChunkBytes + 2 * (N * 2); // values, run counts/starts, run-index marks
 };
 
 // One warp decompresses one partition.  (reference cascaded_decompression_fcn :1106-1435)
@@ -557,12 +742,10 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
 {
   constexpr int N = DecompSmem<T>::N;
   constexpr int W = (int)sizeof(T);
-  using P = PArr<T, N>;
-  using PC = PArr<uint16_t, N>;
+  using Z = Swz<T>;
   T* A = reinterpret_cast<T*>(smem);
-  T* B = reinterpret_cast<T*>(smem + P::BYTES);
-  uint16_t* C = reinterpret_cast<uint16_t*>(smem + 2 * P::BYTES);
-  uint16_t* I = reinterpret_cast<uint16_t*>(smem + 2 * P::BYTES + PC::BYTES);
+  uint16_t* C = reinterpret_cast<uint16_t*>(smem + kChunkBytes);
+  uint16_t* I = reinterpret_cast<uint16_t*>(smem + kChunkBytes + N * 2);
   const int lane = lane_id();
 
   bool ok = true;
@@ -613,9 +796,7 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
       const size_t final_pos = arrays + off[R];
       if (final_pos + ((final_bytes + 3u) & ~3u) > end) { ok = false; break; }
       int n;
-      T* cur = A;
-      T* oth = B;
-      if (!read_array<T, N>(comp + final_pos, final_bytes, bp != 0, cur, n)) { ok = false; break; }
+      if (!read_array<T, N>(comp + final_pos, final_bytes, bp != 0, A, n)) { ok = false; break; }
       __syncwarp();
       bool wrote_global = false;
       // exact reverse of the encoder's layer order R1 D1 R2 D2 ... (see DESIGN.md on
@@ -624,7 +805,7 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
         if (l < D) {
           if (n + 1 > N) { ok = false; break; }
           const T seed = *reinterpret_cast<const T*>(comp + chunk + delta_off + l * W);
-          delta_decode<T, N>(cur, n, seed);
+          delta_decode<T, N>(A, n, seed);
           n += 1;
         }
         if (l < R) {
@@ -636,23 +817,11 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
             break;
           }
           __syncwarp();
+          // the expansion of the outermost layer goes straight to the output buffer
           const bool last = (l == 0);
-          if (last) {
-            // the expansion of the outermost layer goes straight to the output
-            // buffer, if the partition has room for it
-            uint32_t sum = 0;
-            for (int j = lane; j < n; j += 32) sum += C[PC::p(j)];
-            uint32_t tot;
-            warp_excl_sum<uint32_t>(sum, tot);
-            if (tot > (uint32_t)N || done + tot > n_total) { ok = false; break; }
-          }
-          const int m = rle_decode<T, N>(cur, C, n, I, last ? out + done : oth, last);
+          const int m = rle_expand<T, N>(A, C, n, I, last ? out + done : nullptr, last ? n_total - done : 0);
           if (m < 0) { ok = false; break; }
-          if (last) {
-            wrote_global = true;
-          } else {
-            T* t = cur; cur = oth; oth = t;
-          }
+          wrote_global = last;
           n = m;
         }
       }
@@ -660,7 +829,13 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
       if (done + (size_t)n > n_total) { ok = false; break; }
       if (!wrote_global) {
         T* o = out + done;
-        for (int i = lane; i < n; i += 32) o[i] = cur[P::p(i)];
+        int st = 0;
+        if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+          const int vecs = n / Z::VE;
+          for (int v = lane; v < vecs; v += 32) reinterpret_cast<uint4*>(o)[v] = ld_vec<T>(A, v * Z::VE).q;
+          st = vecs * Z::VE;
+        }
+        for (int i = st + lane; i < n; i += 32) o[i] = A[Z::p(i)];
       }
       done += (size_t)n;
       if (chunk_bytes < (uint32_t)msize) { ok = false; break; }
@@ -675,7 +850,6 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
     if (status_out) *status_out = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
   }
 }
-
 // The element width of the whole batch comes from partition 0's type byte, as in
 // the reference (CascadedBatch.hip:156-168).  One launch per width; the three
 // that do not match return after one load.
