@@ -49,6 +49,9 @@ inline void allow_smem(K kernel, int bytes)
   cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
+// 4, 8, 16 or 32 from an environment variable (tuning knob), else 0.
+int group_lanes_from_env(const char* name);
+
 inline size_t round_up_sz(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---------------------------------------------------------------- device side

@@ -233,14 +233,20 @@ __device__ __forceinline__ bool read_lsic(const uint8_t* comp, uint32_t comp_len
   return true;
 }
 
-// One warp per chunk; every lane parses the (broadcast) token stream, copies are
-// cooperative.  (reference decompressStream, LZ4Kernels.hiph:971-1097)
+// A group of G lanes per chunk (32/G chunks advance per warp instruction); every
+// lane of the group parses the token stream, copies are cooperative within the
+// group.  (reference decompressStream, LZ4Kernels.hiph:971-1097)
+template <int G>
 __global__ void __launch_bounds__(kDecWarps * 32)
 decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
                   void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
 {
-  const size_t stride = (size_t)gridDim.x * kDecWarps;
-  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
+  constexpr int kGroups = 32 / G;
+  const uint32_t sub = (uint32_t)lane_id() & (G - 1);
+  const unsigned gmask = group_mask<G>();
+  const size_t stride = (size_t)gridDim.x * kDecWarps * kGroups;
+  for (size_t chunk = ((size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5)) * kGroups + ((uint32_t)lane_id() / G);
+       chunk < batch; chunk += stride) {
     const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
     uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
     const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
@@ -254,7 +260,7 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const 
       uint32_t nlit = tok >> 4;
       if (nlit == 15 && !read_lsic(comp, comp_len, ci, nlit)) { ok = false; break; }
       if (nlit > cap - di || nlit > comp_len - ci) { ok = false; break; }
-      warp_copy_ro(out + di, comp + ci, nlit);
+      group_copy_ro<G>(out + di, comp + ci, nlit, sub);
       ci += nlit;
       di += nlit;
       if (ci < comp_len) {
@@ -264,18 +270,112 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const 
         uint32_t mlen = 4 + (tok & 15);
         if ((tok & 15) == 15 && !read_lsic(comp, comp_len, ci, mlen)) { ok = false; break; }
         if (off == 0 || off > di || mlen > cap - di) { ok = false; break; }
-        __syncwarp();
-        warp_copy_match(out + di, off, mlen);
+        __syncwarp(gmask);
+        group_copy_match<G>(out + di, off, mlen, sub, gmask);
         di += mlen;
-        __syncwarp();
+        __syncwarp(gmask);
       }
     }
-    if (lane_id() == 0) {
+    if (sub == 0) {
+      if (actual) actual[chunk] = ok ? di : 0;
+      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
+    }
+    __syncwarp(gmask);
+  }
+}
+
+// v3 decoder: one warp per chunk, rounds of up to 32 sequences (lz_common.cuh,
+// "round executor").  Parsing a round touches only the compressed stream, so the
+// dependent chain per sequence is token -> lengths -> next token; the copies of
+// the whole round then run 32 output bytes per step.
+__device__ __forceinline__ bool read_lsic_bounded(const uint8_t* comp, uint32_t comp_len, uint32_t& ci,
+                                                  uint32_t& value)
+{
+  uint32_t b = 0xff;
+  while (b == 0xff) {
+    if (ci >= comp_len || value > 0x7FFFFFFFu) return false;
+    b = __ldg(comp + ci);
+    ++ci;
+    value += b;
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(kDecWarps * 32)
+decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
+                        void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
+{
+  const uint32_t lane = (uint32_t)lane_id();
+  const size_t stride = (size_t)gridDim.x * kDecWarps;
+  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    const size_t cap64 = out_caps[chunk];
+    const uint32_t cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
+    uint32_t ci = 0, di = 0;
+    bool ok = true;
+    while (ok && ci < comp_len) {
+      // ---- parse up to 32 sequences; lane k keeps sequence k
+      uint32_t my_nlit = 0, my_mlen = 0, my_off = 0, my_lp = 0;
+      for (uint32_t k = 0; k < 32 && ci < comp_len; ++k) {
+        const uint32_t tok = __ldg(comp + ci);
+        ++ci;
+        uint32_t nlit = tok >> 4;
+        if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
+        if (nlit > comp_len - ci) { ok = false; break; }
+        const uint32_t lp = ci;
+        ci += nlit;
+        uint32_t mlen = 0, off = 0;
+        if (ci < comp_len) {
+          if (ci + 2 > comp_len) { ok = false; break; }
+          off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
+          ci += 2;
+          mlen = 4 + (tok & 15);
+          if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
+          if (off == 0) { ok = false; break; }
+        }
+        if (lane == k) {
+          my_nlit = nlit;
+          my_mlen = mlen;
+          my_off = off;
+          my_lp = lp;
+        }
+      }
+      if (!ok) break;
+      // ---- place the sequences and validate them
+      uint32_t total;
+      const uint32_t pos = add_sat_u32(di, warp_excl_sum_sat(add_sat_u32(my_nlit, my_mlen), total));
+      const uint32_t lit_end = add_sat_u32(pos, my_nlit);
+      const uint32_t seq_end = add_sat_u32(lit_end, my_mlen);
+      const bool bad = seq_end > cap || (my_mlen != 0 && my_off > lit_end);
+      if (__any_sync(kFull, bad)) { ok = false; break; }
+      const uint32_t end = di + total; // no overflow: every seq_end <= cap
+      execute_round(out, comp, di, end, pos, lit_end, seq_end, my_lp - pos, my_off);
+      di = end;
+    }
+    if (lane == 0) {
       if (actual) actual[chunk] = ok ? di : 0;
       if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
     }
     __syncwarp();
   }
+}
+
+// Lanes per chunk: narrow groups when the batch has enough chunks to fill the
+// machine with them, the whole warp for small batches.  B200COMP_LZ4_DEC_G overrides.
+// B200COMP_LZ4_DEC_G = 4/8/16/32 selects the v2 sub-warp-group decoder (kept for
+// comparison and for its tests); the default is the round decoder.
+static bool use_group_decoder() { return group_lanes_from_env("B200COMP_LZ4_DEC_G") != 0; }
+
+static int decode_group_lanes(size_t batch)
+{
+  const int forced = group_lanes_from_env("B200COMP_LZ4_DEC_G");
+  if (forced) return forced;
+  const size_t warps = (size_t)sm_count() * 16;
+  if (batch >= warps * 4) return 8;
+  if (batch >= warps * 2) return 16;
+  return 32;
 }
 
 // Size-only walk: one thread per chunk.
@@ -422,11 +522,30 @@ hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compr
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
-  const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
+  if (!lz4::use_group_decoder()) {
+    const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
+    const size_t cap = (size_t)sm_count() * 16;
+    lz4::decompress_round_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
+        device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
+        device_actual_uncompressed_bytes, device_statuses, batch_size);
+    return check_launch(fn);
+  }
+  const int g = lz4::decode_group_lanes(batch_size);
+  const size_t per_cta = (size_t)lz4::kDecWarps * (32 / g);
+  const size_t need = (batch_size + per_cta - 1) / per_cta;
   const size_t cap = (size_t)sm_count() * 16;
-  lz4::decompress_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
-      device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
-      device_actual_uncompressed_bytes, device_statuses, batch_size);
+  const int grid = (int)(need < cap ? need : cap);
+#define B200_LZ4_DEC(G)                                                                                            \
+  lz4::decompress_kernel<G><<<grid, lz4::kDecWarps * 32, 0, stream>>>(                                             \
+      device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,        \
+      device_actual_uncompressed_bytes, device_statuses, batch_size)
+  switch (g) {
+  case 4: B200_LZ4_DEC(4); break;
+  case 8: B200_LZ4_DEC(8); break;
+  case 16: B200_LZ4_DEC(16); break;
+  default: B200_LZ4_DEC(32); break;
+  }
+#undef B200_LZ4_DEC
   return check_launch(fn);
 }
 

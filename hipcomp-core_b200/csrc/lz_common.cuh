@@ -89,3 +89,219 @@ __device__ __forceinline__ void warp_copy_match(uint8_t* dst, uint32_t off, uint
 }
 
 } // namespace b200comp
+
+// ---------------------------------------------------------------- sub-warp groups
+//
+// The decoders give each chunk to a group of G lanes (G = 4..32, a power of two), so
+// that one warp instruction advances 32/G chunks at once: typical LZ sequences move
+// 5-20 bytes, which leaves most of a 32-lane copy idle.  Everything below is
+// synchronised with the group's own lane mask only.
+
+namespace b200comp {
+
+template <int G>
+__device__ __forceinline__ unsigned group_mask()
+{
+  if (G == 32) return kFull;
+  return ((1u << (G & 31)) - 1u) << ((unsigned)lane_id() & ~(unsigned)(G - 1));
+}
+
+// n bytes of read-only memory -> dst, by the G lanes of a group (sub = lane % G).
+template <int G>
+__device__ __forceinline__ void group_copy_ro(uint8_t* dst, const uint8_t* src, uint32_t n, uint32_t sub)
+{
+  if (n < 16u * G) {
+    for (uint32_t i = sub; i < n; i += G) dst[i] = __ldg(src + i);
+    return;
+  }
+  const uint32_t head = (uint32_t)((16 - (reinterpret_cast<uintptr_t>(dst) & 15)) & 15);
+  for (uint32_t i = sub; i < head; i += G) dst[i] = __ldg(src + i);
+  dst += head;
+  src += head;
+  n -= head;
+  const uint32_t vecs = n >> 4;
+  const uintptr_t sa = reinterpret_cast<uintptr_t>(src);
+  const uint32_t* sw = reinterpret_cast<const uint32_t*>(sa & ~(uintptr_t)3);
+  const uint32_t sh = (uint32_t)(sa & 3) * 8;
+  uint4* dv = reinterpret_cast<uint4*>(dst);
+  if (sh == 0) {
+    for (uint32_t v = sub; v < vecs; v += G) {
+      const uint32_t* s = sw + 4 * v;
+      uint4 r;
+      r.x = __ldg(s); r.y = __ldg(s + 1); r.z = __ldg(s + 2); r.w = __ldg(s + 3);
+      dv[v] = r;
+    }
+  } else {
+    for (uint32_t v = sub; v < vecs; v += G) {
+      const uint32_t* s = sw + 4 * v;
+      const uint32_t a = __ldg(s), b = __ldg(s + 1), c = __ldg(s + 2), d = __ldg(s + 3), e = __ldg(s + 4);
+      uint4 r;
+      r.x = __funnelshift_r(a, b, sh);
+      r.y = __funnelshift_r(b, c, sh);
+      r.z = __funnelshift_r(c, d, sh);
+      r.w = __funnelshift_r(d, e, sh);
+      dv[v] = r;
+    }
+  }
+  for (uint32_t i = (vecs << 4) + sub; i < n; i += G) dst[i] = __ldg(src + i);
+}
+
+// LZ77 match copy by a group: dst[i] = dst[i - off], i in [0, len), sequential-copy
+// semantics.  Earlier writes of the group are visible (caller synchronised).
+template <int G>
+__device__ __forceinline__ void group_copy_match(uint8_t* dst, uint32_t off, uint32_t len, uint32_t sub,
+                                                 unsigned gmask)
+{
+  const uint8_t* src = dst - off;
+  if (off >= 16u * G && len >= 16u * G) {
+    // 16 bytes per lane and step; a step only reads bytes stored by earlier steps
+    const uint32_t head = (uint32_t)((16 - (reinterpret_cast<uintptr_t>(dst) & 15)) & 15);
+    for (uint32_t i = sub; i < head; i += G) dst[i] = src[i]; // head < 16 <= off: no overlap inside
+    __syncwarp(gmask);
+    const uint32_t n = len - head;
+    const uint32_t vecs = n >> 4;
+    uint8_t* d0 = dst + head;
+    const uintptr_t sa = reinterpret_cast<uintptr_t>(src + head);
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(sa & ~(uintptr_t)3);
+    const uint32_t sh = (uint32_t)(sa & 3) * 8;
+    uint4* dv = reinterpret_cast<uint4*>(d0);
+    const bool overlap = off < len;
+    for (uint32_t base = 0; base < vecs; base += G) {
+      const uint32_t v = base + sub;
+      if (v < vecs) {
+        const uint32_t* s = sw + 4 * v;
+        const uint32_t a = s[0], b = s[1], c = s[2], d = s[3];
+        uint4 r;
+        if (sh == 0) {
+          r = make_uint4(a, b, c, d);
+        } else {
+          const uint32_t e = s[4]; // bytes below d0 + 16 v + 16 - off + 3 < this step's first store
+          r.x = __funnelshift_r(a, b, sh);
+          r.y = __funnelshift_r(b, c, sh);
+          r.z = __funnelshift_r(c, d, sh);
+          r.w = __funnelshift_r(d, e, sh);
+        }
+        dv[v] = r;
+      }
+      if (overlap) __syncwarp(gmask);
+    }
+    for (uint32_t i = (vecs << 4) + sub; i < n; i += G) d0[i] = (d0 - off)[i]; // tail < 16 <= off
+    return;
+  }
+  if (off >= len) {
+    for (uint32_t i = sub; i < len; i += G) dst[i] = src[i];
+  } else if (off >= (uint32_t)G) {
+    for (uint32_t base = 0; base < len; base += G) {
+      const uint32_t i = base + sub;
+      if (i < len) dst[i] = src[i];
+      __syncwarp(gmask);
+    }
+  } else {
+    // period `off` < G, all pattern bytes precede dst
+    uint32_t idx = sub % off;
+    const uint32_t step = (uint32_t)G % off;
+    for (uint32_t i = sub; i < len; i += G) {
+      dst[i] = src[idx];
+      idx += step;
+      if (idx >= off) idx -= off;
+    }
+  }
+}
+
+} // namespace b200comp
+
+// ---------------------------------------------------------------- round executor
+//
+// The v3 decoders split a chunk's work into rounds of up to 32 elements.  The token
+// stream of a round is parsed first (a short dependent chain that only touches the
+// compressed bytes); after that every lane holds one element
+//     output [pos, lit_end)   <- literals  comp[p + lit_delta]
+//     output [lit_end, end)   <- match     out[p - off]
+// and the warp produces the round's output span strictly in address order, 32
+// consecutive bytes per step: lane t finds the element that owns byte b + t, loads
+// its source byte and stores it.  A match byte is ready when its source lies below
+// the step's first byte (everything below is complete); the step is cut in front of
+// the first byte that is not.  Stores of a step are 32 consecutive bytes.
+namespace b200comp {
+
+__device__ __forceinline__ uint32_t add_sat_u32(uint32_t a, uint32_t b)
+{
+  const uint32_t s = a + b;
+  return s < a ? 0xFFFFFFFFu : s;
+}
+
+// exclusive prefix sum over the warp, saturating at 2^32 - 1
+__device__ __forceinline__ uint32_t warp_excl_sum_sat(uint32_t v, uint32_t& total)
+{
+  uint32_t incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(kFull, incl, d);
+    if (lane_id() >= d) incl = add_sat_u32(incl, o);
+  }
+  total = __shfl_sync(kFull, incl, 31);
+  const uint32_t prev = __shfl_up_sync(kFull, incl, 1);
+  return lane_id() == 0 ? 0u : prev;
+}
+
+constexpr uint32_t kLongRun = 96; // a segment this long leaves the byte-per-lane loop
+
+__device__ __forceinline__ void execute_round(uint8_t* out, const uint8_t* comp, uint32_t begin, uint32_t end,
+                                              uint32_t pos, uint32_t lit_end, uint32_t seq_end,
+                                              uint32_t lit_delta, uint32_t off)
+{
+  const uint32_t lane = (uint32_t)lane_id();
+  const unsigned le_mask = 0xFFFFFFFFu >> (31u - lane); // bits 0..lane
+  uint32_t b = begin, carry = 0;
+  while (b < end) {
+    const uint32_t rel = pos - b; // elements that started below b wrap to a large value
+    const unsigned starts = __reduce_or_sync(kFull, (rel < 32u && seq_end > pos) ? (1u << rel) : 0u);
+    const uint32_t own = carry + (uint32_t)__popc(starts & le_mask) - 1u;
+    const uint32_t o_lit_end = __shfl_sync(kFull, lit_end, (int)own);
+    const uint32_t o_off = __shfl_sync(kFull, off, (int)own);
+    const uint32_t o_delta = __shfl_sync(kFull, lit_delta, (int)own);
+    if ((starts & ~1u) == 0u) {
+      // one element owns the whole step: long literal / match runs move as vectors
+      const uint32_t o_seq_end = __shfl_sync(kFull, seq_end, (int)own);
+      const bool in_lit = b < o_lit_end;
+      const uint32_t seg_end = in_lit ? o_lit_end : o_seq_end;
+      if (seg_end - b >= kLongRun) {
+        if (in_lit)
+          group_copy_ro<32>(out + b, comp + (uint32_t)(b + o_delta), seg_end - b, lane);
+        else
+          group_copy_match<32>(out + b, o_off, seg_end - b, lane, kFull);
+        b = seg_end;
+        carry += (starts & 1u);
+        __syncwarp();
+        continue;
+      }
+    }
+    const uint32_t p = b + lane;
+    const bool active = p < end;
+    const bool is_lit = p < o_lit_end;
+    uint32_t q = p - o_off;
+    bool ready = is_lit || q < b;
+    if (active && !ready) {
+      // source inside this step: fold it back by whole periods if that stays inside
+      // the match's own source window [lit_end - off, ...)
+      const uint32_t n = (q - b) / o_off + 1u;
+      const uint32_t q2 = q - n * o_off;
+      if (q2 + o_off >= o_lit_end) {
+        q = q2;
+        ready = true;
+      }
+    }
+    const unsigned blocked = __ballot_sync(kFull, active && !ready);
+    const uint32_t limit = blocked ? (uint32_t)__ffs((int)blocked) - 1u : 32u;
+    if (active && lane < limit) {
+      const uint8_t* src = is_lit ? comp + (uint32_t)(p + o_delta) : out + q;
+      out[p] = *src;
+    }
+    const uint32_t adv = min(limit, end - b);
+    carry += (uint32_t)__popc(starts & (adv >= 32u ? 0xFFFFFFFFu : ((1u << adv) - 1u)));
+    b += adv;
+    __syncwarp();
+  }
+}
+
+} // namespace b200comp

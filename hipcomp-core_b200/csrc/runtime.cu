@@ -2,6 +2,7 @@
 #include "common.cuh"
 
 #include <atomic>
+#include <cstdlib>
 
 namespace b200comp {
 
@@ -17,6 +18,14 @@ int sm_count()
     cache[dev].store(v, std::memory_order_relaxed);
   }
   return v;
+}
+
+int group_lanes_from_env(const char* name)
+{
+  const char* v = std::getenv(name);
+  if (!v) return 0;
+  const int g = std::atoi(v);
+  return (g == 4 || g == 8 || g == 16 || g == 32) ? g : 0;
 }
 
 } // namespace b200comp

@@ -185,12 +185,18 @@ __device__ __forceinline__ bool read_preamble(const uint8_t* comp, uint32_t comp
   return true;
 }
 
+// A group of G lanes per chunk, 32/G chunks per warp (see lz_common.cuh).
+template <int G>
 __global__ void __launch_bounds__(kDecWarps * 32)
 decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
                   void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
 {
-  const size_t stride = (size_t)gridDim.x * kDecWarps;
-  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
+  constexpr int kGroups = 32 / G;
+  const uint32_t sub = (uint32_t)lane_id() & (G - 1);
+  const unsigned gmask = group_mask<G>();
+  const size_t stride = (size_t)gridDim.x * kDecWarps * kGroups;
+  for (size_t chunk = ((size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5)) * kGroups + ((uint32_t)lane_id() / G);
+       chunk < batch; chunk += stride) {
     const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
     uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
     const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
@@ -230,9 +236,9 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const 
             cur += 5;
           }
           if (offset == 0 || offset > dst || left < blen) { ok = false; break; }
-          __syncwarp();
-          warp_copy_match(out + dst, offset, blen);
-          __syncwarp();
+          __syncwarp(gmask);
+          group_copy_match<G>(out + dst, offset, blen, sub, gmask);
+          __syncwarp(gmask);
         } else {
           blen = b0 >> 2;
           cur += 1;
@@ -246,19 +252,29 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const 
           if (blen == 0xffffffffu) { ok = false; break; }
           blen += 1;
           if (left < blen || blen > comp_len - cur) { ok = false; break; }
-          warp_copy_ro(out + dst, comp + cur, blen);
+          group_copy_ro<G>(out + dst, comp + cur, blen, sub);
           cur += blen;
         }
         dst += blen;
         left -= blen;
       }
     }
-    if (lane_id() == 0) {
+    if (sub == 0) {
       if (actual) actual[chunk] = size - left;
       if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
     }
-    __syncwarp();
+    __syncwarp(gmask);
   }
+}
+
+static int decode_group_lanes(size_t batch)
+{
+  const int forced = group_lanes_from_env("B200COMP_SNAPPY_DEC_G");
+  if (forced) return forced;
+  const size_t warps = (size_t)sm_count() * 16;
+  if (batch >= warps * 4) return 8;
+  if (batch >= warps * 2) return 16;
+  return 32;
 }
 
 __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, size_t* sizes, size_t batch)
@@ -317,11 +333,22 @@ hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_co
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
   if (batch_size == 0) return hipcompSuccess;
-  const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
+  const int g = snappy::decode_group_lanes(batch_size);
+  const size_t per_cta = (size_t)snappy::kDecWarps * (32 / g);
+  const size_t need = (batch_size + per_cta - 1) / per_cta;
   const size_t cap = (size_t)sm_count() * 16;
-  snappy::decompress_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
-      device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
-      device_actual_uncompressed_bytes, device_statuses, batch_size);
+  const int grid = (int)(need < cap ? need : cap);
+#define B200_SNAPPY_DEC(G)                                                                                         \
+  snappy::decompress_kernel<G><<<grid, snappy::kDecWarps * 32, 0, stream>>>(                                       \
+      device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,          \
+      device_actual_uncompressed_bytes, device_statuses, batch_size)
+  switch (g) {
+  case 4: B200_SNAPPY_DEC(4); break;
+  case 8: B200_SNAPPY_DEC(8); break;
+  case 16: B200_SNAPPY_DEC(16); break;
+  default: B200_SNAPPY_DEC(32); break;
+  }
+#undef B200_SNAPPY_DEC
   return check_launch(fn);
 }
 
