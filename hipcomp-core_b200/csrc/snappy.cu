@@ -267,6 +267,102 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const 
   }
 }
 
+// v3 decoder: one warp per chunk, rounds of up to 32 elements (literal or copy),
+// executed by the in-order round executor of lz_common.cuh.  An element that fails
+// validation ends the stream; the elements in front of it are still produced, so
+// the reported progress equals the sequential decoder's (size - bytes_left).
+__global__ void __launch_bounds__(kDecWarps * 32)
+decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
+                        void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
+{
+  const uint32_t lane = (uint32_t)lane_id();
+  const size_t stride = (size_t)gridDim.x * kDecWarps;
+  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    const size_t cap64 = out_caps[chunk];
+    uint32_t size = 0, cur = 0, left = 0;
+    bool ok = comp_len != 0 && comp != nullptr;
+    if (ok) ok = read_preamble(comp, comp_len, cur, size);
+    if (ok) {
+      const size_t cap = cap64 == 0 ? size : cap64;
+      if ((cur >= comp_len && size != 0) || size > cap) ok = false;
+    }
+    if (!ok) size = 0;
+    if (ok) {
+      left = size;
+      uint32_t dst = 0;
+      while (ok && left > 0) {
+        // ---- parse up to 32 elements; lane k keeps element k
+        uint32_t my_len = 0, my_off = 0, my_lp = 0; // my_off == 0: literal
+        uint32_t pdst = dst;                        // output position while parsing
+        for (uint32_t k = 0; k < 32 && left > 0; ++k) {
+          if (cur >= comp_len) { ok = false; break; }
+          const uint32_t b0 = __ldg(comp + cur);
+          uint32_t blen, offset = 0, lp = 0;
+          if (b0 & 3) {
+            if ((b0 & 3) == 1) {
+              if (cur + 2 > comp_len) { ok = false; break; }
+              offset = ((b0 & 0xe0) << 3) | __ldg(comp + cur + 1);
+              blen = ((b0 >> 2) & 7) + 4;
+              cur += 2;
+            } else if ((b0 & 3) == 2) {
+              if (cur + 3 > comp_len) { ok = false; break; }
+              offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8);
+              blen = (b0 >> 2) + 1;
+              cur += 3;
+            } else {
+              if (cur + 5 > comp_len) { ok = false; break; }
+              offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8)
+                       | ((uint32_t)__ldg(comp + cur + 3) << 16) | ((uint32_t)__ldg(comp + cur + 4) << 24);
+              blen = (b0 >> 2) + 1;
+              cur += 5;
+            }
+            if (offset == 0 || offset > pdst || left < blen) { ok = false; break; }
+          } else {
+            blen = b0 >> 2;
+            cur += 1;
+            if (blen >= 60) {
+              const uint32_t nb = blen - 59;
+              if (cur + nb > comp_len) { ok = false; break; }
+              blen = 0;
+              for (uint32_t i = 0; i < nb; ++i) blen |= (uint32_t)__ldg(comp + cur + i) << (8 * i);
+              cur += nb;
+            }
+            if (blen == 0xffffffffu) { ok = false; break; }
+            blen += 1;
+            if (left < blen || blen > comp_len - cur) { ok = false; break; }
+            lp = cur;
+            cur += blen;
+          }
+          if (lane == k) {
+            my_len = blen;
+            my_off = offset;
+            my_lp = lp;
+          }
+          pdst += blen;
+          left -= blen;
+        }
+        // ---- run the elements parsed so far (all of them validated)
+        uint32_t total;
+        const uint32_t pos = dst + warp_excl_sum_sat(my_len, total); // total <= size: no saturation
+        const uint32_t seq_end = pos + my_len;
+        const uint32_t lit_end = my_off == 0 ? seq_end : pos;
+        execute_round(out, comp, dst, dst + total, pos, lit_end, seq_end, my_lp - pos, my_off);
+        dst += total;
+      }
+    }
+    if (lane == 0) {
+      if (actual) actual[chunk] = size - left;
+      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
+    }
+    __syncwarp();
+  }
+}
+
+static bool use_group_decoder() { return group_lanes_from_env("B200COMP_SNAPPY_DEC_G") != 0; }
+
 static int decode_group_lanes(size_t batch)
 {
   const int forced = group_lanes_from_env("B200COMP_SNAPPY_DEC_G");
@@ -333,6 +429,14 @@ hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_co
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
   if (batch_size == 0) return hipcompSuccess;
+  if (!snappy::use_group_decoder()) {
+    const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
+    const size_t cap = (size_t)sm_count() * 16;
+    snappy::decompress_round_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
+        device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
+        device_actual_uncompressed_bytes, device_statuses, batch_size);
+    return check_launch(fn);
+  }
   const int g = snappy::decode_group_lanes(batch_size);
   const size_t per_cta = (size_t)snappy::kDecWarps * (32 / g);
   const size_t need = (batch_size + per_cta - 1) / per_cta;

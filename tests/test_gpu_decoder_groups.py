@@ -1,4 +1,5 @@
-"""-m gpu: the LZ4 / Snappy decoders at every sub-warp group width (4, 8, 16, 32 lanes per chunk).
+"""-m gpu: the LZ4 / Snappy decoders in every variant: the default round decoder (width 0 below)
+and the sub-warp group decoder at 4, 8, 16, 32 lanes per chunk.
 
 The width is normally picked from the batch size; B200COMP_{LZ4,SNAPPY}_DEC_G forces it so that every
 template instance sees the same inputs: ragged sizes, periodic data with every period 1..40 (overlapping
@@ -23,6 +24,11 @@ def _g():
     return gpu_common
 
 
+def _force(codec, width):
+    if width:
+        os.environ[ENV[codec]] = str(width)
+
+
 def periodic_chunks(n):
     rng = np.random.default_rng(99)
     out = []
@@ -39,8 +45,10 @@ def periodic_chunks(n):
     return out
 
 
-@pytest.fixture(params=[4, 8, 16, 32])
+@pytest.fixture(params=[0, 4, 8, 16, 32])
 def width(request):
+    for v in ENV.values():
+        os.environ.pop(v, None)
     yield request.param
     for v in ENV.values():
         os.environ.pop(v, None)
@@ -49,7 +57,7 @@ def width(request):
 @pytest.mark.parametrize("codec", ["lz4", "snappy"])
 def test_roundtrip_every_group_width(codec, width):
     g = _g()
-    os.environ[ENV[codec]] = str(width)
+    _force(codec, width)
     for max_chunk, chunks in ((9000, periodic_chunks(9000)), (65536, datagen.mixed_chunks(65536, 13, 5)),
                               (2048, [c[: (37 * i) % 2049] for i, c in enumerate(datagen.mixed_chunks(2048, 67, 8))])):
         comp, dec, status, sizes, actual = g.roundtrip(codec, chunks, max_chunk=max_chunk)
@@ -62,7 +70,7 @@ def test_lz4_stock_and_corrupt_streams_every_group_width(width):
     g = _g()
     from test_oracle_lz4 import stock_compress
 
-    os.environ[ENV["lz4"]] = str(width)
+    _force("lz4", width)
     chunks = periodic_chunks(5000) + datagen.mixed_chunks(4096, 12, 3)
     comp = [stock_compress(c) for c in chunks]
     out, actual, status = g.decode_raw("lz4", comp, [len(c) for c in chunks])
@@ -99,7 +107,7 @@ def test_snappy_stock_and_corrupt_streams_every_group_width(width):
     g = _g()
     import pyarrow as pa
 
-    os.environ[ENV["snappy"]] = str(width)
+    _force("snappy", width)
     codec = pa.Codec("snappy")
     chunks = periodic_chunks(5000) + datagen.mixed_chunks(4096, 12, 3)
     comp = [np.frombuffer(codec.compress(c.tobytes()).to_pybytes(), np.uint8) for c in chunks]
