@@ -10,6 +10,7 @@
 // literal runs move as 16-byte vectors.  The decoder bounds every compressed
 // read (the reference's does not).
 #include "lz_common.cuh"
+#include "lz_pipeline.cuh"
 
 #pragma GCC visibility push(default)
 #include "hipcomp/lz4.h"
@@ -315,25 +316,61 @@ decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, 
     const uint32_t cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
     uint32_t ci = 0, di = 0;
     bool ok = true;
+    uint32_t win = 0, wpos = 0, wvalid = 0; // register window: stream bytes [wpos, wpos + wvalid)
+    const uintptr_t comp_end_al = (reinterpret_cast<uintptr_t>(comp + comp_len) + 3) & ~(uintptr_t)3;
     while (ok && ci < comp_len) {
-      // ---- parse up to 32 sequences; lane k keeps sequence k
+      // ---- parse up to 32 sequences; lane k keeps sequence k.  Tokens are read from a
+      //      64-byte register window over the stream (lane j holds bytes [2j, 2j+4) of it,
+      //      so one shuffle fetches up to three bytes at any position): no address
+      //      arithmetic and no cache access on the token -> lengths -> next-token chain.
       uint32_t my_nlit = 0, my_mlen = 0, my_off = 0, my_lp = 0;
       for (uint32_t k = 0; k < 32 && ci < comp_len; ++k) {
-        const uint32_t tok = __ldg(comp + ci);
-        ++ci;
-        uint32_t nlit = tok >> 4;
-        if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
-        if (nlit > comp_len - ci) { ok = false; break; }
-        const uint32_t lp = ci;
-        ci += nlit;
-        uint32_t mlen = 0, off = 0;
-        if (ci < comp_len) {
-          if (ci + 2 > comp_len) { ok = false; break; }
-          off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
-          ci += 2;
-          mlen = 4 + (tok & 15);
-          if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
-          if (off == 0) { ok = false; break; }
+        if (ci - wpos + 17u > wvalid && wpos + wvalid != comp_len) {
+          const uintptr_t a = reinterpret_cast<uintptr_t>(comp + ci);
+          const uint32_t mis = (uint32_t)(a & 3);
+          const uint32_t* w = reinterpret_cast<const uint32_t*>(a - mis);
+          uint32_t word = 0;
+          if (lane < 18u && reinterpret_cast<uintptr_t>(w + lane) < comp_end_al) word = __ldg(w + lane);
+          const uint32_t o = mis + 2u * lane;
+          const uint32_t lo = __shfl_sync(kFull, word, (int)(o >> 2));
+          const uint32_t hi = __shfl_sync(kFull, word, (int)(o >> 2) + 1);
+          win = __funnelshift_r(lo, hi, (o & 3u) * 8u);
+          wpos = ci;
+          wvalid = min(64u, comp_len - ci);
+        }
+        const uint32_t idx = ci - wpos;
+        uint32_t nlit, mlen = 0, off = 0, lp;
+        bool fast = false;
+        if (idx < wvalid) {
+          const uint32_t tok = (__shfl_sync(kFull, win, (int)(idx >> 1)) >> ((idx & 1u) * 8u)) & 0xffu;
+          nlit = tok >> 4;
+          const uint32_t mc = tok & 15u;
+          const uint32_t oidx = idx + 1u + nlit;
+          if (nlit < 15u && mc < 15u && oidx + 2u <= wvalid) {
+            off = (__shfl_sync(kFull, win, (int)(oidx >> 1)) >> ((oidx & 1u) * 8u)) & 0xffffu;
+            if (off == 0) { ok = false; break; }
+            lp = ci + 1u;
+            mlen = mc + 4u;
+            ci += nlit + 3u;
+            fast = true;
+          }
+        }
+        if (!fast) {
+          const uint32_t tok = __ldg(comp + ci);
+          ++ci;
+          nlit = tok >> 4;
+          if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
+          if (nlit > comp_len - ci) { ok = false; break; }
+          lp = ci;
+          ci += nlit;
+          if (ci < comp_len) {
+            if (ci + 2 > comp_len) { ok = false; break; }
+            off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
+            ci += 2;
+            mlen = 4 + (tok & 15);
+            if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
+            if (off == 0) { ok = false; break; }
+          }
         }
         if (lane == k) {
           my_nlit = nlit;
@@ -364,9 +401,58 @@ decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, 
 
 // Lanes per chunk: narrow groups when the batch has enough chunks to fill the
 // machine with them, the whole warp for small batches.  B200COMP_LZ4_DEC_G overrides.
+// v4 decoder (lz_pipeline.cuh): LZ4 token walk for one parse lane.
+struct PipeCodec {
+  struct State {
+    const uint8_t* comp;
+    uint32_t comp_len, cap, ci, di;
+  };
+  __device__ static void open(State& s, const uint8_t* comp, uint32_t comp_len, size_t cap64)
+  {
+    s.comp = comp;
+    s.comp_len = comp_len;
+    s.cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
+    s.ci = 0;
+    s.di = 0;
+  }
+  __device__ static uint32_t out_pos(const State& s) { return s.di; }
+  __device__ static uint32_t result(const State& s, bool ok) { return ok ? s.di : 0u; }
+  __device__ static int step(State& s, pipe::Desc& d)
+  {
+    uint32_t ci = s.ci;
+    const uint32_t comp_len = s.comp_len;
+    if (ci >= comp_len) return pipe::kDone;
+    const uint8_t* comp = s.comp;
+    const uint32_t tok = __ldg(comp + ci);
+    ++ci;
+    uint32_t nlit = tok >> 4;
+    if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) return pipe::kFail;
+    if (nlit > comp_len - ci || nlit > s.cap - s.di) return pipe::kFail;
+    const uint32_t lp = ci;
+    const uint32_t lit_end = s.di + nlit;
+    ci += nlit;
+    uint32_t mlen = 0, off = 0;
+    if (ci < comp_len) {
+      if (ci + 2 > comp_len) return pipe::kFail;
+      off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
+      ci += 2;
+      mlen = 4 + (tok & 15);
+      if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) return pipe::kFail;
+      if (off == 0 || off > lit_end || mlen > s.cap - lit_end) return pipe::kFail;
+    }
+    d.pos = s.di;
+    d.lit_end = lit_end;
+    d.lp = lp;
+    d.off = off;
+    s.ci = ci;
+    s.di = lit_end + mlen;
+    return pipe::kToken;
+  }
+};
+
 // B200COMP_LZ4_DEC_G = 4/8/16/32 selects the v2 sub-warp-group decoder (kept for
 // comparison and for its tests); the default is the round decoder.
-static bool use_group_decoder() { return group_lanes_from_env("B200COMP_LZ4_DEC_G") != 0; }
+static int decoder_variant() { return decoder_variant_from_env("B200COMP_LZ4_DEC_G"); }
 
 static int decode_group_lanes(size_t batch)
 {
@@ -522,7 +608,16 @@ hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compr
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
-  if (!lz4::use_group_decoder()) {
+  const int variant = lz4::decoder_variant();
+  if (variant == kDecoderPipeline) {
+    const size_t need = (batch_size + pipe::kExecWarps - 1) / pipe::kExecWarps;
+    const size_t cap = (size_t)sm_count() * pipe::kCtasPerSm;
+    pipe::decompress_pipeline_kernel<lz4::PipeCodec><<<(int)(need < cap ? need : cap), pipe::kThreads, 0, stream>>>(
+        device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
+        device_actual_uncompressed_bytes, device_statuses, batch_size);
+    return check_launch(fn);
+  }
+  if (variant == kDecoderDefault || variant == kDecoderRound) {
     const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
     const size_t cap = (size_t)sm_count() * 16;
     lz4::decompress_round_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(

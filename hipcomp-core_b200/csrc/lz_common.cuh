@@ -253,6 +253,38 @@ __device__ __forceinline__ void execute_round(uint8_t* out, const uint8_t* comp,
   const uint32_t lane = (uint32_t)lane_id();
   const unsigned le_mask = 0xFFFFFFFFu >> (31u - lane); // bits 0..lane
   uint32_t b = begin, carry = 0;
+  // Round without internal dependencies (every match source ends below `begin`, the
+  // common case for text whose matches reach kilobytes back) and without long runs:
+  // steps need no ordering, so two of them are in flight per iteration and their
+  // loads overlap.
+  const bool far = seq_end == lit_end || (lit_end - off) + (seq_end - lit_end) <= begin;
+  const bool plain = far && (seq_end - pos) < kLongRun;
+  if (__all_sync(kFull, plain)) {
+    while (b < end) {
+      const uint32_t rel = pos - b;
+      const bool mine = seq_end > pos;
+      const unsigned s0 = __reduce_or_sync(kFull, (rel < 32u && mine) ? (1u << rel) : 0u);
+      const unsigned s1 = __reduce_or_sync(kFull, (rel - 32u < 32u && mine) ? (1u << (rel - 32u)) : 0u);
+      const uint32_t c1 = carry + (uint32_t)__popc(s0);
+      const uint32_t own0 = carry + (uint32_t)__popc(s0 & le_mask) - 1u;
+      const uint32_t own1 = c1 + (uint32_t)__popc(s1 & le_mask) - 1u;
+      const uint32_t le0 = __shfl_sync(kFull, lit_end, (int)own0), le1 = __shfl_sync(kFull, lit_end, (int)(own1 & 31u));
+      const uint32_t of0 = __shfl_sync(kFull, off, (int)own0), of1 = __shfl_sync(kFull, off, (int)(own1 & 31u));
+      const uint32_t dl0 = __shfl_sync(kFull, lit_delta, (int)own0), dl1 = __shfl_sync(kFull, lit_delta, (int)(own1 & 31u));
+      const uint32_t p0 = b + lane, p1 = p0 + 32u;
+      const uint8_t* a0 = p0 < le0 ? comp + (uint32_t)(p0 + dl0) : out + (p0 - of0);
+      const uint8_t* a1 = p1 < le1 ? comp + (uint32_t)(p1 + dl1) : out + (p1 - of1);
+      uint8_t v0 = 0, v1 = 0;
+      if (p0 < end) v0 = *a0;
+      if (p1 < end) v1 = *a1;
+      if (p0 < end) out[p0] = v0;
+      if (p1 < end) out[p1] = v1;
+      carry = c1 + (uint32_t)__popc(s1);
+      b += 64u;
+    }
+    __syncwarp();
+    return;
+  }
   while (b < end) {
     const uint32_t rel = pos - b; // elements that started below b wrap to a large value
     const unsigned starts = __reduce_or_sync(kFull, (rel < 32u && seq_end > pos) ? (1u << rel) : 0u);

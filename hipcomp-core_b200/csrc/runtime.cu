@@ -3,6 +3,7 @@
 
 #include <atomic>
 #include <cstdlib>
+#include <cstring>
 
 namespace b200comp {
 
@@ -26,6 +27,16 @@ int group_lanes_from_env(const char* name)
   if (!v) return 0;
   const int g = std::atoi(v);
   return (g == 4 || g == 8 || g == 16 || g == 32) ? g : 0;
+}
+
+int decoder_variant_from_env(const char* name)
+{
+  const char* v = std::getenv(name);
+  if (!v || !*v) return kDecoderDefault;
+  if (std::strcmp(v, "pipe") == 0) return kDecoderPipeline;
+  if (std::strcmp(v, "round") == 0) return kDecoderRound;
+  const int g = std::atoi(v);
+  return (g == 4 || g == 8 || g == 16 || g == 32) ? g : kDecoderDefault;
 }
 
 } // namespace b200comp

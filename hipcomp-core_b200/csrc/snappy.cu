@@ -9,6 +9,7 @@
 // element grammar of src/snappy/decompression_decode.hiph:72-150 (the reference
 // uses a 3-warp prefetch/decode/process pipeline with nanosleep spin queues).
 #include "lz_common.cuh"
+#include "lz_pipeline.cuh"
 
 #pragma GCC visibility push(default)
 #include "hipcomp/snappy.h"
@@ -293,14 +294,68 @@ decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, 
     if (ok) {
       left = size;
       uint32_t dst = 0;
+      uint32_t win = 0, wpos = 0, wvalid = 0; // register window: stream bytes [wpos, wpos + wvalid)
+      const uintptr_t comp_end_al = (reinterpret_cast<uintptr_t>(comp + comp_len) + 3) & ~(uintptr_t)3;
       while (ok && left > 0) {
         // ---- parse up to 32 elements; lane k keeps element k
         uint32_t my_len = 0, my_off = 0, my_lp = 0; // my_off == 0: literal
         uint32_t pdst = dst;                        // output position while parsing
         for (uint32_t k = 0; k < 32 && left > 0; ++k) {
           if (cur >= comp_len) { ok = false; break; }
-          const uint32_t b0 = __ldg(comp + cur);
+          // 64-byte register window over the stream (lane j holds bytes [2j, 2j+4)): one
+          // shuffle yields a tag and its two following bytes.
+          if (cur - wpos + 3u > wvalid && wpos + wvalid != comp_len) {
+            const uintptr_t a = reinterpret_cast<uintptr_t>(comp + cur);
+            const uint32_t mis = (uint32_t)(a & 3);
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(a - mis);
+            uint32_t word = 0;
+            if (lane < 18u && reinterpret_cast<uintptr_t>(w + lane) < comp_end_al) word = __ldg(w + lane);
+            const uint32_t o = mis + 2u * lane;
+            const uint32_t lo = __shfl_sync(kFull, word, (int)(o >> 2));
+            const uint32_t hi = __shfl_sync(kFull, word, (int)(o >> 2) + 1);
+            win = __funnelshift_r(lo, hi, (o & 3u) * 8u);
+            wpos = cur;
+            wvalid = min(64u, comp_len - cur);
+          }
+          const uint32_t idx = cur - wpos;
           uint32_t blen, offset = 0, lp = 0;
+          if (idx + 3u <= wvalid) {
+            const uint32_t t3 = __shfl_sync(kFull, win, (int)(idx >> 1)) >> ((idx & 1u) * 8u);
+            const uint32_t tag = t3 & 0xffu, kind = t3 & 3u;
+            if (kind == 1u || kind == 2u) {
+              if (kind == 1u) {
+                offset = ((tag & 0xe0u) << 3) | ((t3 >> 8) & 0xffu);
+                blen = ((tag >> 2) & 7u) + 4u;
+                cur += 2;
+              } else {
+                offset = (t3 >> 8) & 0xffffu;
+                blen = (tag >> 2) + 1u;
+                cur += 3;
+              }
+              if (offset == 0 || offset > pdst || left < blen) { ok = false; cur = wpos + idx; break; }
+              if (lane == k) {
+                my_len = blen;
+                my_off = offset;
+              }
+              pdst += blen;
+              left -= blen;
+              continue;
+            }
+            if (kind == 0u && tag < (60u << 2)) {
+              blen = (tag >> 2) + 1u;
+              if (left < blen || blen > comp_len - (cur + 1u)) { ok = false; break; }
+              if (lane == k) {
+                my_len = blen;
+                my_off = 0;
+                my_lp = cur + 1u;
+              }
+              cur += 1u + blen;
+              pdst += blen;
+              left -= blen;
+              continue;
+            }
+          }
+          const uint32_t b0 = __ldg(comp + cur);
           if (b0 & 3) {
             if ((b0 & 3) == 1) {
               if (cur + 2 > comp_len) { ok = false; break; }
@@ -361,7 +416,88 @@ decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, 
   }
 }
 
-static bool use_group_decoder() { return group_lanes_from_env("B200COMP_SNAPPY_DEC_G") != 0; }
+// v4 decoder (lz_pipeline.cuh): Snappy element walk for one parse lane.
+struct PipeCodec {
+  struct State {
+    const uint8_t* comp;
+    uint32_t comp_len, cur, size, left;
+    bool bad;
+  };
+  __device__ static void open(State& s, const uint8_t* comp, uint32_t comp_len, size_t cap64)
+  {
+    s.comp = comp;
+    s.comp_len = comp_len;
+    s.cur = 0;
+    s.size = 0;
+    bool ok = comp_len != 0 && comp != nullptr;
+    if (ok) ok = read_preamble(comp, comp_len, s.cur, s.size);
+    if (ok) {
+      const size_t cap = cap64 == 0 ? s.size : cap64;
+      if ((s.cur >= comp_len && s.size != 0) || s.size > cap) ok = false;
+    }
+    if (!ok) s.size = 0;
+    s.left = s.size;
+    s.bad = !ok;
+  }
+  __device__ static uint32_t out_pos(const State& s) { return s.size - s.left; }
+  __device__ static uint32_t result(const State& s, bool) { return s.size - s.left; }
+  __device__ static int step(State& s, pipe::Desc& d)
+  {
+    if (s.bad) return pipe::kFail;
+    if (s.left == 0) return pipe::kDone;
+    uint32_t cur = s.cur;
+    const uint32_t comp_len = s.comp_len;
+    if (cur >= comp_len) return pipe::kFail;
+    const uint8_t* comp = s.comp;
+    const uint32_t dst = s.size - s.left;
+    const uint32_t b0 = __ldg(comp + cur);
+    uint32_t blen, offset = 0, lp = 0;
+    if (b0 & 3) {
+      if ((b0 & 3) == 1) {
+        if (cur + 2 > comp_len) return pipe::kFail;
+        offset = ((b0 & 0xe0) << 3) | __ldg(comp + cur + 1);
+        blen = ((b0 >> 2) & 7) + 4;
+        cur += 2;
+      } else if ((b0 & 3) == 2) {
+        if (cur + 3 > comp_len) return pipe::kFail;
+        offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8);
+        blen = (b0 >> 2) + 1;
+        cur += 3;
+      } else {
+        if (cur + 5 > comp_len) return pipe::kFail;
+        offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8)
+                 | ((uint32_t)__ldg(comp + cur + 3) << 16) | ((uint32_t)__ldg(comp + cur + 4) << 24);
+        blen = (b0 >> 2) + 1;
+        cur += 5;
+      }
+      if (offset == 0 || offset > dst || s.left < blen) return pipe::kFail;
+    } else {
+      blen = b0 >> 2;
+      cur += 1;
+      if (blen >= 60) {
+        const uint32_t nb = blen - 59;
+        if (cur + nb > comp_len) return pipe::kFail;
+        blen = 0;
+        for (uint32_t i = 0; i < nb; ++i) blen |= (uint32_t)__ldg(comp + cur + i) << (8 * i);
+        cur += nb;
+      }
+      if (blen == 0xffffffffu) return pipe::kFail;
+      blen += 1;
+      if (s.left < blen || blen > comp_len - cur) return pipe::kFail;
+      lp = cur;
+      cur += blen;
+    }
+    d.pos = dst;
+    d.lit_end = offset == 0 ? dst + blen : dst;
+    d.lp = lp;
+    d.off = offset;
+    s.cur = cur;
+    s.left -= blen;
+    return pipe::kToken;
+  }
+};
+
+static int decoder_variant() { return decoder_variant_from_env("B200COMP_SNAPPY_DEC_G"); }
 
 static int decode_group_lanes(size_t batch)
 {
@@ -429,7 +565,17 @@ hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_co
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
   if (batch_size == 0) return hipcompSuccess;
-  if (!snappy::use_group_decoder()) {
+  const int variant = snappy::decoder_variant();
+  if (variant == kDecoderPipeline) {
+    const size_t need = (batch_size + pipe::kExecWarps - 1) / pipe::kExecWarps;
+    const size_t cap = (size_t)sm_count() * pipe::kCtasPerSm;
+    pipe::decompress_pipeline_kernel<snappy::PipeCodec>
+        <<<(int)(need < cap ? need : cap), pipe::kThreads, 0, stream>>>(
+            device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
+            device_actual_uncompressed_bytes, device_statuses, batch_size);
+    return check_launch(fn);
+  }
+  if (variant == kDecoderDefault || variant == kDecoderRound) {
     const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
     const size_t cap = (size_t)sm_count() * 16;
     snappy::decompress_round_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(

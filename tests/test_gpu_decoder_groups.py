@@ -1,5 +1,6 @@
-"""-m gpu: the LZ4 / Snappy decoders in every variant: the default round decoder (width 0 below)
-and the sub-warp group decoder at 4, 8, 16, 32 lanes per chunk.
+"""-m gpu: the LZ4 / Snappy decoders in every variant: the default one-warp round decoder
+(width 0 below), the decoupled parse/exec pipeline decoder ("pipe") and the sub-warp group decoder at
+4, 8, 16, 32 lanes per chunk.
 
 The width is normally picked from the batch size; B200COMP_{LZ4,SNAPPY}_DEC_G forces it so that every
 template instance sees the same inputs: ragged sizes, periodic data with every period 1..40 (overlapping
@@ -45,7 +46,7 @@ def periodic_chunks(n):
     return out
 
 
-@pytest.fixture(params=[0, 4, 8, 16, 32])
+@pytest.fixture(params=[0, "pipe", 4, 8, 16, 32])
 def width(request):
     for v in ENV.values():
         os.environ.pop(v, None)
