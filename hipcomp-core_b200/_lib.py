@@ -46,6 +46,31 @@ for _c, _opts in (("LZ4", LZ4Opts), ("Snappy", SnappyOpts), ("Cascaded", Cascade
     PROTOTYPES[f"hipcompBatched{_c}DecompressAsync"] = [_vp, _vp, _vp, _vp, _sz, _vp, _sz, _vp, _vp, _vp]
     PROTOTYPES[f"hipcompBatched{_c}GetDecompressSizeAsync"] = [_vp, _vp, _vp, _sz, _vp]
 
+# extensions (include/hipcomp/b200_ext.h): gather + the C view of the HLIF managers
+_vpp = C.POINTER(C.c_void_p)
+EXT_PROTOTYPES = {
+    "b200compGatherChunksAsync": [_vp, _vp, _vp, _vp, _sz, _vp],
+    "b200compManagerCreateLZ4": [_sz, C.c_int, _vp, C.c_int, _vpp],
+    "b200compManagerCreateSnappy": [_sz, _vp, C.c_int, _vpp],
+    "b200compManagerCreateCascaded": [C.POINTER(CascadedOpts), _vp, C.c_int, _vpp],
+    "b200compManagerCreateFromBuffer": [_vp, _vp, C.c_int, _vpp],
+    "b200compManagerConfigureCompression": [_vp, _sz, _vpp, _szp, _szp],
+    "b200compManagerCompress": [_vp, _vp, _vp, _vp],
+    "b200compManagerGetCompressedOutputSize": [_vp, _vp, _szp],
+    "b200compManagerConfigureDecompression": [_vp, _vp, _vpp, _szp, _szp],
+    "b200compManagerConfigureDecompressionFromComp": [_vp, _vp, _vpp, _szp, _szp],
+    "b200compManagerDecompress": [_vp, _vp, _vp, _vp],
+    "b200compManagerGetRequiredScratchBufferSize": [_vp, _szp],
+    "b200compManagerSetScratchBuffer": [_vp, _vp],
+    "b200compCompConfigStatus": [_vp],
+    "b200compDecompConfigStatus": [_vp],
+}
+EXT_VOID = {
+    "b200compManagerDestroy": [_vp],
+    "b200compCompConfigDestroy": [_vp],
+    "b200compDecompConfigDestroy": [_vp],
+}
+
 _lib = None
 
 
@@ -74,8 +99,12 @@ def lib():
                 f"{LIB_PATH} is missing: the CUDA library has not been built "
                 "(run __graft_entry__.build()). There is no CPU fallback.")
         _lib = C.CDLL(LIB_PATH)
-        for name, args in PROTOTYPES.items():
+        for name, args in list(PROTOTYPES.items()) + list(EXT_PROTOTYPES.items()):
             fn = getattr(_lib, name)
             fn.restype = C.c_int
+            fn.argtypes = args
+        for name, args in EXT_VOID.items():
+            fn = getattr(_lib, name)
+            fn.restype = None
             fn.argtypes = args
     return _lib

@@ -1,0 +1,680 @@
+// b200comp — high-level interface: LZ4Manager / SnappyManager / CascadedManager + create_manager().
+//
+// Replaces reference src/highlevel/{ManagerBase,BatchManager,LZ4Manager,SnappyManager,
+// CascadedManager}.hpp, {LZ4,Snappy,Cascaded}HlifKernels.hip, CompressionConfigs.cpp,
+// PinnedPtrs.hpp, hipcompManagerFactory.cpp and src/hipcomp_common_deps/hlif_shared.hiph.
+//
+// Container bytes are the reference's: CommonHeader(64) | FormatSpecHeader |
+// pad to 8 | u64 offsets[n] | u64 sizes[n] | u32 comp_checksums[n] | u32 decomp_checksums[n] |
+// chunk data.  What changes is how the data region is produced.  The reference runs one
+// persistent kernel in which every CTA compresses into a private scratch slot, claims
+// output space with an atomicAdd and copies the slot over (chunks land in completion
+// order).  Here the buffer is cut into WAVES of W chunks; each wave is
+//     setup   (pointer / size arrays of the wave, in scratch)
+//     encode  (the same batched kernels the C ABI launches, chunk i -> scratch slot i,
+//              compressed sizes written straight into the container's sizes[] array)
+//     place   (one-CTA exclusive scan of the sizes -> offsets[], running cursor in
+//              CommonHeader::comp_data_size; first wave also fills the header)
+//     gather  (slot i -> data + offsets[i], 16-byte vector copies)
+// so chunks land in index order (deterministic container bytes), no atomics, and every
+// kernel improvement of the low-level path is inherited.  Decompression is setup -> the
+// batched decoder -> a status fold into the config's pinned status word.
+#include "common.cuh"
+#include "workspace.hpp"
+
+#pragma GCC visibility push(default)
+#include "hipcomp/b200_ext.h"
+#include "hipcomp/cascaded.h"
+#include "hipcomp/hipcompManagerFactory.hpp"
+#include "hipcomp/lz4.h"
+#include "hipcomp/snappy.h"
+#pragma GCC visibility pop
+
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <vector>
+
+namespace hipcomp {
+
+// ------------------------------------------------------------------ wire structs
+// reference src/hipcomp_common_deps/hlif_shared_types.hpp:58-84
+enum FormatType : uint8_t { kFmtLZ4 = 0, kFmtSnappy = 1, kFmtANS = 2, kFmtGDeflate = 3, kFmtCascaded = 4, kFmtBitcomp = 5 };
+
+struct CommonHeader {
+  uint32_t magic_number;
+  uint8_t major_version;
+  uint8_t minor_version;
+  uint8_t format;
+  uint64_t comp_data_size;
+  uint64_t decomp_data_size;
+  uint64_t num_chunks;
+  bool include_chunk_starts;
+  uint32_t full_comp_buffer_checksum;
+  uint32_t decomp_buffer_checksum;
+  bool include_per_chunk_comp_buffer_checksums;
+  bool include_per_chunk_decomp_buffer_checksums;
+  uint64_t uncomp_chunk_size;
+  uint32_t comp_data_offset;
+};
+static_assert(sizeof(CommonHeader) == 64, "CommonHeader is a wire format");
+static_assert(offsetof(CommonHeader, comp_data_size) == 8 && offsetof(CommonHeader, num_chunks) == 24
+                  && offsetof(CommonHeader, uncomp_chunk_size) == 48 && offsetof(CommonHeader, comp_data_offset) == 56,
+              "CommonHeader layout");
+
+static void cu_check(cudaError_t e, const char* what)
+{
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    throw std::runtime_error(std::string("hipcomp HLIF: ") + what + ": " + cudaGetErrorString(e));
+  }
+}
+static void st_check(hipcompStatus_t s, const char* what)
+{
+  if (s != hipcompSuccess) throw std::runtime_error(std::string("hipcomp HLIF: ") + what + " failed with status " + std::to_string((int)s));
+}
+
+// ------------------------------------------------------------------ pinned status pool
+// reference src/highlevel/PinnedPtrs.hpp:61-211: pinned host words handed out one at a
+// time, first block of 10, then blocks of 100; a handle returns its word on destruction.
+template <typename T>
+struct PinnedPtrPool {
+  static constexpr size_t kFirst = 10, kNext = 100;
+  std::vector<T*> blocks;
+  std::vector<T*> free_list;
+
+  PinnedPtrPool() { grow(kFirst); }
+  PinnedPtrPool(const PinnedPtrPool&) = delete;
+  PinnedPtrPool& operator=(const PinnedPtrPool&) = delete;
+  ~PinnedPtrPool()
+  {
+    for (T* b : blocks) cudaFreeHost(b);
+  }
+  void grow(size_t n)
+  {
+    T* b = nullptr;
+    cu_check(cudaHostAlloc(reinterpret_cast<void**>(&b), n * sizeof(T), cudaHostAllocDefault), "cudaHostAlloc(status pool)");
+    blocks.push_back(b);
+    for (size_t i = 0; i < n; ++i) free_list.push_back(b + i);
+  }
+  T* take()
+  {
+    if (free_list.empty()) grow(kNext);
+    T* p = free_list.back();
+    free_list.pop_back();
+    return p;
+  }
+  void give(T* p) { free_list.push_back(p); }
+  size_t available() const { return free_list.size(); }
+  size_t capacity() const { return blocks.empty() ? 0 : kFirst + (blocks.size() - 1) * kNext; }
+};
+
+struct StatusHandle {
+  PinnedPtrPool<hipcompStatus_t>& pool;
+  hipcompStatus_t* ptr;
+  explicit StatusHandle(PinnedPtrPool<hipcompStatus_t>& p) : pool(p), ptr(p.take()) { *ptr = hipcompSuccess; }
+  StatusHandle(const StatusHandle&) = delete;
+  ~StatusHandle() { pool.give(ptr); }
+};
+
+// ------------------------------------------------------------------ configs
+// reference src/highlevel/CompressionConfigs.{hpp,cpp}:52-164
+struct CompressionConfig::CompressionConfigImpl {
+  StatusHandle status;
+  explicit CompressionConfigImpl(PinnedPtrPool<hipcompStatus_t>& pool) : status(pool) {}
+};
+
+CompressionConfig::CompressionConfig(PinnedPtrPool<hipcompStatus_t>& pool, size_t uncompressed_buffer_size)
+    : impl(std::make_shared<CompressionConfigImpl>(pool)),
+      uncompressed_buffer_size(uncompressed_buffer_size),
+      max_compressed_buffer_size(0),
+      num_chunks(0)
+{
+}
+hipcompStatus_t* CompressionConfig::get_status() const { return impl->status.ptr; }
+CompressionConfig::~CompressionConfig() {}
+CompressionConfig::CompressionConfig(CompressionConfig&& o)
+    : impl(std::move(o.impl)),
+      uncompressed_buffer_size(o.uncompressed_buffer_size),
+      max_compressed_buffer_size(o.max_compressed_buffer_size),
+      num_chunks(o.num_chunks)
+{
+}
+CompressionConfig::CompressionConfig(const CompressionConfig& o)
+    : impl(o.impl),
+      uncompressed_buffer_size(o.uncompressed_buffer_size),
+      max_compressed_buffer_size(o.max_compressed_buffer_size),
+      num_chunks(o.num_chunks)
+{
+}
+CompressionConfig& CompressionConfig::operator=(const CompressionConfig& o)
+{
+  impl = o.impl;
+  uncompressed_buffer_size = o.uncompressed_buffer_size;
+  max_compressed_buffer_size = o.max_compressed_buffer_size;
+  num_chunks = o.num_chunks;
+  return *this;
+}
+CompressionConfig& CompressionConfig::operator=(CompressionConfig&& o)
+{
+  impl = std::move(o.impl);
+  uncompressed_buffer_size = o.uncompressed_buffer_size;
+  max_compressed_buffer_size = o.max_compressed_buffer_size;
+  num_chunks = o.num_chunks;
+  return *this;
+}
+
+struct DecompressionConfig::DecompressionConfigImpl {
+  StatusHandle status;
+  explicit DecompressionConfigImpl(PinnedPtrPool<hipcompStatus_t>& pool) : status(pool) {}
+};
+
+DecompressionConfig::DecompressionConfig(PinnedPtrPool<hipcompStatus_t>& pool)
+    : impl(std::make_shared<DecompressionConfigImpl>(pool)), decomp_data_size(0), num_chunks(0)
+{
+}
+hipcompStatus_t* DecompressionConfig::get_status() const { return impl->status.ptr; }
+DecompressionConfig::~DecompressionConfig() {}
+DecompressionConfig::DecompressionConfig(DecompressionConfig&& o)
+    : impl(std::move(o.impl)), decomp_data_size(o.decomp_data_size), num_chunks(o.num_chunks)
+{
+}
+DecompressionConfig::DecompressionConfig(const DecompressionConfig& o)
+    : impl(o.impl), decomp_data_size(o.decomp_data_size), num_chunks(o.num_chunks)
+{
+}
+DecompressionConfig& DecompressionConfig::operator=(const DecompressionConfig& o)
+{
+  impl = o.impl;
+  decomp_data_size = o.decomp_data_size;
+  num_chunks = o.num_chunks;
+  return *this;
+}
+DecompressionConfig& DecompressionConfig::operator=(DecompressionConfig&& o)
+{
+  impl = std::move(o.impl);
+  decomp_data_size = o.decomp_data_size;
+  num_chunks = o.num_chunks;
+  return *this;
+}
+
+// ------------------------------------------------------------------ kernels
+namespace {
+
+using b200comp::kFull;
+
+// pointer / size arrays of one compression wave
+__global__ void __launch_bounds__(256)
+setup_compress_kernel(const uint8_t* decomp, size_t decomp_bytes, size_t chunk, size_t wave_start, size_t n,
+                      uint8_t* slots, size_t slot_stride, const void** in_ptrs, size_t* in_bytes, void** out_ptrs)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t begin = (wave_start + i) * chunk;
+    const size_t left = decomp_bytes - begin;
+    in_ptrs[i] = decomp + begin;
+    in_bytes[i] = left < chunk ? left : chunk;
+    out_ptrs[i] = slots + i * slot_stride;
+  }
+}
+
+struct HeaderFill {
+  CommonHeader* header; // null: not the first wave
+  uint8_t format;
+  uint64_t decomp_data_size, num_chunks, uncomp_chunk_size;
+  uint32_t comp_data_offset;
+};
+
+// offsets[i] = cursor + exclusive sum of the (padded) sizes of the wave; cursor += total.
+// One CTA: the scan is a few microseconds next to the encode of the same wave.
+__global__ void __launch_bounds__(1024)
+place_kernel(const size_t* sizes, size_t* offsets, size_t n, unsigned long long* cursor, size_t align, HeaderFill hf)
+{
+  __shared__ unsigned long long warp_tot[32];
+  __shared__ unsigned long long base_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) {
+    base_s = *cursor;
+    if (hf.header) {
+      CommonHeader* h = hf.header;
+      h->magic_number = 0;
+      h->major_version = 2;
+      h->minor_version = 2;
+      h->format = hf.format;
+      h->decomp_data_size = hf.decomp_data_size;
+      h->num_chunks = hf.num_chunks;
+      h->include_chunk_starts = true;
+      h->full_comp_buffer_checksum = 0;
+      h->decomp_buffer_checksum = 0;
+      h->include_per_chunk_comp_buffer_checksums = false;
+      h->include_per_chunk_decomp_buffer_checksums = false;
+      h->uncomp_chunk_size = hf.uncomp_chunk_size;
+      h->comp_data_offset = hf.comp_data_offset;
+    }
+  }
+  __syncthreads();
+  unsigned long long base = base_s;
+  for (size_t tile = 0; tile < n; tile += 1024) {
+    const size_t i = tile + threadIdx.x;
+    unsigned long long v = 0;
+    if (i < n) v = (sizes[i] + align - 1) / align * align;
+    unsigned long long incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long o = __shfl_up_sync(kFull, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      unsigned long long w = warp_tot[lane], wi = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long o = __shfl_up_sync(kFull, wi, d);
+        if (lane >= d) wi += o;
+      }
+      warp_tot[lane] = wi - w; // exclusive
+      if (lane == 31) base_s = base + wi;
+    }
+    __syncthreads();
+    if (i < n) offsets[i] = base + warp_tot[warp] + (incl - v);
+    base = base_s;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *cursor = base;
+}
+
+__global__ void __launch_bounds__(256)
+setup_decompress_kernel(const uint8_t* data, const size_t* offsets, uint8_t* decomp, size_t decomp_bytes, size_t chunk,
+                        size_t wave_start, size_t n, const void** comp_ptrs, void** out_ptrs, size_t* out_caps)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t g = wave_start + i;
+    const size_t begin = g * chunk;
+    const size_t left = begin < decomp_bytes ? decomp_bytes - begin : 0;
+    comp_ptrs[i] = data + offsets[g];
+    out_ptrs[i] = decomp + begin;
+    out_caps[i] = left < chunk ? left : chunk;
+  }
+}
+
+// any failed chunk -> the config's pinned status word (reference hlif_shared.hiph:332-337)
+__global__ void __launch_bounds__(256)
+fold_status_kernel(const hipcompStatus_t* statuses, size_t n, hipcompStatus_t* out)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const hipcompStatus_t s = statuses[i];
+    if (s != hipcompSuccess) *out = s;
+  }
+}
+
+inline int grid_for(size_t n, int block)
+{
+  const size_t need = (n + block - 1) / block;
+  const size_t cap = (size_t)b200comp::sm_count() * 8;
+  return (int)(need < cap ? (need ? need : 1) : cap);
+}
+
+template <typename T>
+inline T* align8(T* p)
+{
+  return reinterpret_cast<T*>((reinterpret_cast<uintptr_t>(p) + 7) & ~(uintptr_t)7);
+}
+
+} // namespace
+
+// ------------------------------------------------------------------ the manager
+// One class plays the reference's ManagerBase<F> + BatchManager<F>
+// (src/highlevel/ManagerBase.hpp:80-324, BatchManager.hpp:71-281); a codec supplies the
+// format header and the two batched calls.
+namespace {
+
+size_t wave_bytes_target()
+{
+  // uncompressed bytes per wave; the scratch buffer scales with it (B200COMP_HLIF_WAVE_MIB)
+  const char* v = std::getenv("B200COMP_HLIF_WAVE_MIB");
+  const long mib = v ? std::atol(v) : 0;
+  return (size_t)(mib > 0 ? mib : 1024) << 20;
+}
+
+class BatchManager : public hipcompManagerBase
+{
+public:
+  BatchManager(size_t uncomp_chunk_size, hipStream_t stream, int device_id)
+      : chunk_(uncomp_chunk_size), stream_(stream), device_id_(device_id)
+  {
+    if (chunk_ == 0) throw std::invalid_argument("hipcomp HLIF: uncompressed chunk size must be > 0");
+    cu_check(cudaHostAlloc(reinterpret_cast<void**>(&header_host_), sizeof(CommonHeader) + 64, cudaHostAllocDefault),
+             "cudaHostAlloc(header)");
+  }
+  ~BatchManager() override
+  {
+    scratch_.release();
+    cudaFreeHost(header_host_);
+  }
+  BatchManager(const BatchManager&) = delete;
+  BatchManager& operator=(const BatchManager&) = delete;
+
+  // ---- codec hooks
+  virtual uint8_t format() const = 0;
+  virtual const void* format_header() const = 0;
+  virtual size_t format_header_bytes() const = 0;
+  virtual size_t max_comp_chunk() const = 0;
+  virtual size_t comp_temp_bytes(size_t n) const = 0;
+  virtual size_t chunk_align() const { return 1; }
+  virtual void batch_compress(const void* const* in_ptrs, const size_t* in_bytes, size_t n, void* temp, size_t temp_bytes,
+                              void* const* out_ptrs, size_t* out_bytes) = 0;
+  virtual void batch_decompress(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
+                                size_t* actual, size_t n, void* const* out_ptrs, hipcompStatus_t* statuses) = 0;
+
+  // ---- hipcompManagerBase
+  CompressionConfig configure_compression(const size_t decomp_buffer_size) final
+  {
+    CompressionConfig cfg{status_pool_, decomp_buffer_size};
+    cfg.num_chunks = (decomp_buffer_size + chunk_ - 1) / chunk_;
+    // true layout (the reference budgets 4 B per size entry, BatchManager.hpp:213-224)
+    cfg.max_compressed_buffer_size = sizeof(CommonHeader) + format_header_bytes() + 8 + cfg.num_chunks * (8 + 8 + 4 + 4)
+                                     + cfg.num_chunks * slot_stride_;
+    return cfg;
+  }
+
+  void compress(const uint8_t* decomp_buffer, uint8_t* comp_buffer, const CompressionConfig& cfg) final
+  {
+    ensure_scratch();
+    const size_t n = cfg.num_chunks;
+    CommonHeader* header = reinterpret_cast<CommonHeader*>(comp_buffer);
+    uint8_t* fmt = comp_buffer + sizeof(CommonHeader);
+    cu_check(cudaMemcpyAsync(fmt, format_header(), format_header_bytes(), cudaMemcpyHostToDevice, stream_), "copy format header");
+    cu_check(cudaMemsetAsync(&header->comp_data_size, 0, sizeof(uint64_t), stream_), "reset comp_data_size");
+    size_t* offsets = align8(reinterpret_cast<size_t*>(fmt + format_header_bytes()));
+    size_t* sizes = offsets + n;
+    uint8_t* data = reinterpret_cast<uint8_t*>(sizes + n) + 8 * n; // two u32 checksum arrays, never filled
+    cu_check(cudaMemsetAsync(sizes + n, 0, 8 * n, stream_), "zero checksums");
+
+    HeaderFill hf{header, format(), cfg.uncompressed_buffer_size, n, chunk_, (uint32_t)(data - comp_buffer)};
+    unsigned long long* cursor = reinterpret_cast<unsigned long long*>(&header->comp_data_size);
+    if (n == 0) {
+      place_kernel<<<1, 1024, 0, stream_>>>(sizes, offsets, 0, cursor, 1, hf);
+      cu_check(cudaGetLastError(), "place_kernel");
+      return;
+    }
+    scratch_.rewind();
+    uint8_t* slots = scratch_.reserve<uint8_t>(wave_ * slot_stride_);
+    const size_t temp_bytes = comp_temp_bytes(wave_);
+    uint8_t* temp = scratch_.reserve<uint8_t>(temp_bytes);
+    const void** in_ptrs = scratch_.reserve<const void*>(wave_);
+    size_t* in_bytes = scratch_.reserve<size_t>(wave_);
+    void** out_ptrs = scratch_.reserve<void*>(wave_);
+    for (size_t start = 0; start < n; start += wave_) {
+      const size_t m = n - start < wave_ ? n - start : wave_;
+      setup_compress_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(decomp_buffer, cfg.uncompressed_buffer_size, chunk_, start,
+                                                                  m, slots, slot_stride_, in_ptrs, in_bytes, out_ptrs);
+      batch_compress(in_ptrs, in_bytes, m, temp, temp_bytes, out_ptrs, sizes + start);
+      place_kernel<<<1, 1024, 0, stream_>>>(sizes + start, offsets + start, m, cursor, chunk_align(), hf);
+      hf.header = nullptr;
+      st_check(b200compGatherChunksAsync(out_ptrs, sizes + start, offsets + start, data, m, stream_), "gather");
+    }
+    cu_check(cudaGetLastError(), "compress launches");
+    (void)cfg.get_status(); // encoders cannot fail per chunk: status stays hipcompSuccess
+  }
+
+  DecompressionConfig configure_decompression(const uint8_t* comp_buffer) final
+  {
+    // The reference copies two header words asynchronously into the config it then returns by
+    // value (ManagerBase.hpp:164-168) and asks the caller to synchronise; here the header is read
+    // with one blocking copy so the returned config is complete.
+    DecompressionConfig cfg{status_pool_};
+    cu_check(cudaMemcpyAsync(header_host_, comp_buffer, sizeof(CommonHeader), cudaMemcpyDeviceToHost, stream_), "read header");
+    cu_check(cudaStreamSynchronize(stream_), "sync");
+    cfg.decomp_data_size = header_host_->decomp_data_size;
+    cfg.num_chunks = (uint32_t)header_host_->num_chunks;
+    return cfg;
+  }
+
+  DecompressionConfig configure_decompression(const CompressionConfig& comp_config) final
+  {
+    DecompressionConfig cfg{status_pool_};
+    cfg.decomp_data_size = comp_config.uncompressed_buffer_size;
+    cfg.num_chunks = (uint32_t)comp_config.num_chunks;
+    return cfg;
+  }
+
+  void decompress(uint8_t* decomp_buffer, const uint8_t* comp_buffer, const DecompressionConfig& cfg) final
+  {
+    ensure_scratch();
+    const size_t n = cfg.num_chunks;
+    if (n == 0) return;
+    const uint8_t* fmt = comp_buffer + sizeof(CommonHeader);
+    const size_t* offsets = align8(reinterpret_cast<const size_t*>(fmt + format_header_bytes()));
+    const size_t* sizes = offsets + n;
+    const uint8_t* data = reinterpret_cast<const uint8_t*>(sizes + n) + 8 * n;
+    scratch_.rewind();
+    const void** comp_ptrs = scratch_.reserve<const void*>(dwave_);
+    void** out_ptrs = scratch_.reserve<void*>(dwave_);
+    size_t* out_caps = scratch_.reserve<size_t>(dwave_);
+    size_t* actual = scratch_.reserve<size_t>(dwave_);
+    hipcompStatus_t* statuses = scratch_.reserve<hipcompStatus_t>(dwave_);
+    for (size_t start = 0; start < n; start += dwave_) {
+      const size_t m = n - start < dwave_ ? n - start : dwave_;
+      setup_decompress_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(data, offsets, decomp_buffer, cfg.decomp_data_size,
+                                                                    chunk_, start, m, comp_ptrs, out_ptrs, out_caps);
+      batch_decompress(comp_ptrs, sizes + start, out_caps, actual, m, out_ptrs, statuses);
+      fold_status_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(statuses, m, cfg.get_status());
+    }
+    cu_check(cudaGetLastError(), "decompress launches");
+  }
+
+  void set_scratch_buffer(uint8_t* new_scratch_buffer) final { scratch_.adopt(new_scratch_buffer, scratch_bytes_); }
+  size_t get_required_scratch_buffer_size() final { return scratch_bytes_; }
+
+  size_t get_compressed_output_size(uint8_t* comp_buffer) final
+  {
+    cu_check(cudaMemcpy(header_host_, comp_buffer, sizeof(CommonHeader), cudaMemcpyDefault), "read header");
+    return header_host_->comp_data_size + header_host_->comp_data_offset;
+  }
+
+protected:
+  // Called at the end of the concrete constructor (reference BatchManager::finish_init).
+  void finish_init()
+  {
+    slot_stride_ = b200comp::round_up_sz(max_comp_chunk(), 16);
+    size_t w = wave_bytes_target() / chunk_;
+    if (w < 64) w = 64;
+    if (w > (1u << 20)) w = 1u << 20;
+    wave_ = w;
+    dwave_ = 1u << 20;
+    using W = b200comp::Workspace;
+    const size_t comp_need = W::footprint<uint8_t>(wave_ * slot_stride_) + W::footprint<uint8_t>(comp_temp_bytes(wave_))
+                             + 3 * W::footprint<size_t>(wave_);
+    const size_t decomp_need = 4 * W::footprint<size_t>(dwave_) + W::footprint<hipcompStatus_t>(dwave_);
+    scratch_bytes_ = comp_need > decomp_need ? comp_need : decomp_need;
+  }
+
+  size_t chunk_;
+  hipStream_t stream_;
+  int device_id_;
+
+private:
+  void ensure_scratch()
+  {
+    if (!scratch_.valid()) scratch_.acquire(scratch_bytes_, stream_);
+  }
+
+  CommonHeader* header_host_ = nullptr;
+  PinnedPtrPool<hipcompStatus_t> status_pool_;
+  b200comp::Workspace scratch_;
+  size_t scratch_bytes_ = 0, slot_stride_ = 0, wave_ = 0, dwave_ = 0;
+};
+
+// ---- LZ4 (reference src/highlevel/LZ4Manager.hpp:67-174)
+class LZ4BatchManager final : public BatchManager
+{
+public:
+  LZ4BatchManager(size_t chunk, hipcompType_t data_type, hipStream_t stream, int device_id)
+      : BatchManager(chunk, stream, device_id)
+  {
+    spec_.data_type = data_type;
+    opts_.data_type = data_type;
+    st_check(hipcompBatchedLZ4CompressGetMaxOutputChunkSize(chunk, opts_, &max_comp_), "LZ4 GetMaxOutputChunkSize");
+    finish_init();
+  }
+  uint8_t format() const override { return kFmtLZ4; }
+  const void* format_header() const override { return &spec_; }
+  size_t format_header_bytes() const override { return sizeof(LZ4FormatSpecHeader); }
+  size_t max_comp_chunk() const override { return max_comp_; }
+  size_t comp_temp_bytes(size_t n) const override
+  {
+    size_t t = 0;
+    st_check(hipcompBatchedLZ4CompressGetTempSize(n, chunk_, opts_, &t), "LZ4 CompressGetTempSize");
+    return t;
+  }
+  void batch_compress(const void* const* in_ptrs, const size_t* in_bytes, size_t n, void* temp, size_t temp_bytes,
+                      void* const* out_ptrs, size_t* out_bytes) override
+  {
+    st_check(hipcompBatchedLZ4CompressAsync(in_ptrs, in_bytes, chunk_, n, temp, temp_bytes, out_ptrs, out_bytes, opts_, stream_),
+             "LZ4 CompressAsync");
+  }
+  void batch_decompress(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps, size_t* actual,
+                        size_t n, void* const* out_ptrs, hipcompStatus_t* statuses) override
+  {
+    st_check(hipcompBatchedLZ4DecompressAsync(comp_ptrs, comp_bytes, out_caps, actual, n, nullptr, 0, out_ptrs, statuses, stream_),
+             "LZ4 DecompressAsync");
+  }
+
+private:
+  LZ4FormatSpecHeader spec_{};
+  hipcompBatchedLZ4Opts_t opts_{};
+  size_t max_comp_ = 0;
+};
+
+// ---- Snappy (reference src/highlevel/SnappyManager.hpp:65-151)
+class SnappyBatchManager final : public BatchManager
+{
+public:
+  SnappyBatchManager(size_t chunk, hipStream_t stream, int device_id) : BatchManager(chunk, stream, device_id)
+  {
+    st_check(hipcompBatchedSnappyCompressGetMaxOutputChunkSize(chunk, hipcompBatchedSnappyDefaultOpts, &max_comp_),
+             "Snappy GetMaxOutputChunkSize");
+    finish_init();
+  }
+  uint8_t format() const override { return kFmtSnappy; }
+  const void* format_header() const override { return &spec_; }
+  size_t format_header_bytes() const override { return sizeof(SnappyFormatSpecHeader); } // empty struct: 1 byte
+  size_t max_comp_chunk() const override { return max_comp_; }
+  size_t comp_temp_bytes(size_t) const override { return 0; }
+  void batch_compress(const void* const* in_ptrs, const size_t* in_bytes, size_t n, void* temp, size_t temp_bytes,
+                      void* const* out_ptrs, size_t* out_bytes) override
+  {
+    st_check(hipcompBatchedSnappyCompressAsync(in_ptrs, in_bytes, chunk_, n, temp, temp_bytes, out_ptrs, out_bytes,
+                                               hipcompBatchedSnappyDefaultOpts, stream_),
+             "Snappy CompressAsync");
+  }
+  void batch_decompress(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps, size_t* actual,
+                        size_t n, void* const* out_ptrs, hipcompStatus_t* statuses) override
+  {
+    st_check(hipcompBatchedSnappyDecompressAsync(comp_ptrs, comp_bytes, out_caps, actual, n, nullptr, 0, out_ptrs, statuses,
+                                                 stream_),
+             "Snappy DecompressAsync");
+  }
+
+private:
+  SnappyFormatSpecHeader spec_{};
+  size_t max_comp_ = 0;
+};
+
+// ---- Cascaded (reference src/highlevel/CascadedManager.hpp:65-165): one manager chunk
+//      (options.chunk_size bytes) is one batched-Cascaded partition.
+class CascadedBatchManager final : public BatchManager
+{
+public:
+  CascadedBatchManager(const hipcompBatchedCascadedOpts_t& options, hipStream_t stream, int device_id)
+      : BatchManager(options.chunk_size, stream, device_id)
+  {
+    std::memset(&spec_, 0, sizeof(spec_)); // padding bytes of the options struct go on the wire
+    spec_.options.chunk_size = options.chunk_size;
+    spec_.options.type = options.type;
+    spec_.options.num_RLEs = options.num_RLEs;
+    spec_.options.num_deltas = options.num_deltas;
+    spec_.options.use_bp = options.use_bp;
+    st_check(hipcompBatchedCascadedCompressGetMaxOutputChunkSize(chunk_, spec_.options, &max_comp_),
+             "Cascaded GetMaxOutputChunkSize");
+    finish_init();
+  }
+  uint8_t format() const override { return kFmtCascaded; }
+  const void* format_header() const override { return &spec_; }
+  size_t format_header_bytes() const override { return sizeof(CascadedFormatSpecHeader); }
+  size_t max_comp_chunk() const override { return max_comp_; }
+  size_t comp_temp_bytes(size_t) const override { return 0; }
+  size_t chunk_align() const override { return 8; } // partitions are read as words of the element type
+  void batch_compress(const void* const* in_ptrs, const size_t* in_bytes, size_t n, void* temp, size_t temp_bytes,
+                      void* const* out_ptrs, size_t* out_bytes) override
+  {
+    st_check(hipcompBatchedCascadedCompressAsync(in_ptrs, in_bytes, chunk_, n, temp, temp_bytes, out_ptrs, out_bytes,
+                                                 spec_.options, stream_),
+             "Cascaded CompressAsync");
+  }
+  void batch_decompress(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps, size_t* actual,
+                        size_t n, void* const* out_ptrs, hipcompStatus_t* statuses) override
+  {
+    st_check(hipcompBatchedCascadedDecompressAsync(comp_ptrs, comp_bytes, out_caps, actual, n, nullptr, 0, out_ptrs,
+                                                   statuses, stream_),
+             "Cascaded DecompressAsync");
+  }
+
+private:
+  CascadedFormatSpecHeader spec_;
+  size_t max_comp_ = 0;
+};
+
+} // namespace
+
+LZ4Manager::LZ4Manager(size_t uncomp_chunk_size, hipcompType_t data_type, hipStream_t user_stream, const int device_id)
+{
+  impl = std::make_unique<LZ4BatchManager>(uncomp_chunk_size, data_type, user_stream, device_id);
+}
+LZ4Manager::~LZ4Manager() {}
+
+SnappyManager::SnappyManager(size_t uncomp_chunk_size, hipStream_t user_stream, int device_id)
+{
+  impl = std::make_unique<SnappyBatchManager>(uncomp_chunk_size, user_stream, device_id);
+}
+SnappyManager::~SnappyManager() {}
+
+CascadedManager::CascadedManager(const hipcompBatchedCascadedOpts_t& options, hipStream_t user_stream, int device_id)
+{
+  impl = std::make_unique<CascadedBatchManager>(options, user_stream, device_id);
+}
+CascadedManager::~CascadedManager() {}
+
+// reference src/highlevel/hipcompManagerFactory.cpp:65-148
+std::shared_ptr<hipcompManagerBase> create_manager(const uint8_t* comp_buffer, hipStream_t stream, const int device_id)
+{
+  struct {
+    CommonHeader common;
+    uint8_t spec[32];
+  } host;
+  cu_check(cudaMemcpyAsync(&host, comp_buffer, sizeof(CommonHeader) + sizeof(CascadedFormatSpecHeader), cudaMemcpyDeviceToHost,
+                           stream),
+           "read container header");
+  cu_check(cudaStreamSynchronize(stream), "sync");
+  switch (host.common.format) {
+  case kFmtLZ4: {
+    LZ4FormatSpecHeader spec;
+    std::memcpy(&spec, host.spec, sizeof(spec));
+    return std::make_shared<LZ4Manager>(host.common.uncomp_chunk_size, spec.data_type, stream, device_id);
+  }
+  case kFmtSnappy:
+    return std::make_shared<SnappyManager>(host.common.uncomp_chunk_size, stream, device_id);
+  case kFmtCascaded: {
+    CascadedFormatSpecHeader spec;
+    std::memcpy(&spec, host.spec, sizeof(spec));
+    return std::make_shared<CascadedManager>(spec.options, stream, device_id);
+  }
+  case kFmtANS:
+  case kFmtGDeflate:
+  case kFmtBitcomp:
+    throw std::runtime_error("hipcomp create_manager: ANS / GDeflate / Bitcomp containers are not supported by this build");
+  default:
+    throw std::runtime_error("hipcomp create_manager: unknown container format " + std::to_string((int)host.common.format));
+  }
+}
+} // namespace hipcomp

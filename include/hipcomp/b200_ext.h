@@ -25,6 +25,50 @@ hipcompStatus_t b200compGatherChunksAsync(
     size_t batch_size,
     hipStream_t stream);
 
+
+/* ---- C view of the high-level managers (hipcomp.hpp classes), for C / FFI callers.
+ * A manager handle wraps hipcomp::LZ4Manager / SnappyManager / CascadedManager or the
+ * result of hipcomp::create_manager(); a config handle wraps CompressionConfig /
+ * DecompressionConfig.  C++ exceptions are mapped to status codes at this boundary
+ * (message on stderr), as the reference's LLIF does (src/Check.cpp:81-101). */
+typedef struct b200compManager b200compManager;
+typedef struct b200compCompConfig b200compCompConfig;
+typedef struct b200compDecompConfig b200compDecompConfig;
+
+hipcompStatus_t b200compManagerCreateLZ4(size_t uncomp_chunk_size, hipcompType_t data_type, hipStream_t stream,
+                                         int device_id, b200compManager** out);
+hipcompStatus_t b200compManagerCreateSnappy(size_t uncomp_chunk_size, hipStream_t stream, int device_id,
+                                            b200compManager** out);
+/* opts: pointer to the batched Cascaded options struct of cascaded.h */
+hipcompStatus_t b200compManagerCreateCascaded(const void* opts, hipStream_t stream, int device_id,
+                                              b200compManager** out);
+/* hipcomp::create_manager(): sniffs the container header (blocking) */
+hipcompStatus_t b200compManagerCreateFromBuffer(const void* device_comp_buffer, hipStream_t stream, int device_id,
+                                                b200compManager** out);
+void b200compManagerDestroy(b200compManager* m);
+
+hipcompStatus_t b200compManagerConfigureCompression(b200compManager* m, size_t uncompressed_bytes,
+                                                    b200compCompConfig** out, size_t* max_compressed_bytes,
+                                                    size_t* num_chunks);
+hipcompStatus_t b200compManagerCompress(b200compManager* m, const void* device_uncompressed,
+                                        void* device_compressed, const b200compCompConfig* cfg);
+hipcompStatus_t b200compManagerGetCompressedOutputSize(b200compManager* m, void* device_compressed, size_t* bytes);
+hipcompStatus_t b200compManagerConfigureDecompression(b200compManager* m, const void* device_compressed,
+                                                      b200compDecompConfig** out, size_t* decomp_bytes,
+                                                      size_t* num_chunks);
+hipcompStatus_t b200compManagerConfigureDecompressionFromComp(b200compManager* m, const b200compCompConfig* comp,
+                                                              b200compDecompConfig** out, size_t* decomp_bytes,
+                                                              size_t* num_chunks);
+hipcompStatus_t b200compManagerDecompress(b200compManager* m, void* device_uncompressed,
+                                          const void* device_compressed, const b200compDecompConfig* cfg);
+hipcompStatus_t b200compManagerGetRequiredScratchBufferSize(b200compManager* m, size_t* bytes);
+hipcompStatus_t b200compManagerSetScratchBuffer(b200compManager* m, void* device_scratch);
+/* value of the config's pinned status word (synchronise the stream first) */
+hipcompStatus_t b200compCompConfigStatus(const b200compCompConfig* cfg);
+hipcompStatus_t b200compDecompConfigStatus(const b200compDecompConfig* cfg);
+void b200compCompConfigDestroy(b200compCompConfig* cfg);
+void b200compDecompConfigDestroy(b200compDecompConfig* cfg);
+
 /* "major.minor.patch (sm_100a)" */
 const char* b200compVersionString(void);
 

@@ -103,3 +103,31 @@ def test_empty_batches_succeed_without_a_device():
         assert getattr(lib, f"hipcompBatched{c}CompressAsync")(dummy, dummy, 0, 0, None, 0, dummy, dummy, o, None) == 0
         assert getattr(lib, f"hipcompBatched{c}DecompressAsync")(dummy, dummy, dummy, dummy, 0, None, 0, dummy, dummy,
                                                                  None) == 0
+
+
+def test_library_exports_the_hlif_classes():
+    """C++ side of the boundary: manager ctors/dtors, config special members, factory."""
+    out = subprocess.check_output(["nm", "-DC", "--defined-only", L.LIB_PATH], text=True)
+    for sym in ("hipcomp::LZ4Manager::LZ4Manager(", "hipcomp::LZ4Manager::~LZ4Manager(",
+                "hipcomp::SnappyManager::SnappyManager(", "hipcomp::CascadedManager::CascadedManager(",
+                "hipcomp::CascadedManager::~CascadedManager(", "hipcomp::create_manager(",
+                "hipcomp::CompressionConfig::CompressionConfig(", "hipcomp::CompressionConfig::get_status(",
+                "hipcomp::DecompressionConfig::DecompressionConfig(", "hipcomp::DecompressionConfig::get_status("):
+        assert sym in out, f"{sym} not exported"
+
+
+def test_public_headers_compile_as_plain_cxx_and_c(tmp_path):
+    """A caller's translation unit: C++14 against the .hpp headers, C99 against the .h headers."""
+    inc = ["-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "include", "hipcomp"), "-I", "/usr/local/cuda/include"]
+    cxx = tmp_path / "user.cpp"
+    cxx.write_text('#include "hipcomp/hipcompManagerFactory.hpp"\n#include "hipcomp/lz4.h"\n#include "hipcomp/snappy.h"\n'
+                   '#include "hipcomp/cascaded.h"\n#include "hipcomp/b200_ext.h"\n'
+                   "size_t f(hipcomp::hipcompManagerBase& m, const uint8_t* in, uint8_t* out, size_t n) {\n"
+                   "  auto cfg = m.configure_compression(n); m.compress(in, out, cfg);\n"
+                   "  return m.get_compressed_output_size(out); }\n"
+                   "hipcomp::LZ4Manager* g() { return new hipcomp::LZ4Manager(65536, HIPCOMP_TYPE_CHAR); }\n")
+    subprocess.check_call(["g++", "-std=c++14", "-fsyntax-only", *inc, str(cxx)])
+    c = tmp_path / "user.c"
+    c.write_text('#include "hipcomp/lz4.h"\n#include "hipcomp/snappy.h"\n#include "hipcomp/cascaded.h"\n'
+                 '#include "hipcomp/b200_ext.h"\nint main(void) { size_t t; return (int)hipcompBatchedLZ4DecompressGetTempSize(1, 1, &t); }\n')
+    subprocess.check_call(["gcc", "-std=c99", "-fsyntax-only", *inc, str(c)])
