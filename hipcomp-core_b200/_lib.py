@@ -62,6 +62,12 @@ EXT_PROTOTYPES = {
     "b200compManagerDecompress": [_vp, _vp, _vp, _vp],
     "b200compManagerGetRequiredScratchBufferSize": [_vp, _szp],
     "b200compManagerSetScratchBuffer": [_vp, _vp],
+    "b200compRleRequiredWorkspaceSize": [_sz, C.c_int, C.c_int, _szp],
+    "b200compRleCompress": [_vp, _sz, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _sz, _vp],
+    "b200compRleCompressDownstream": [_vp, _sz, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _sz, _vp],
+    "b200compDeltaCompress": [C.c_int, _vp, _vp, _vp, _sz, _vp],
+    "b200compBitPackRequiredWorkspaceSize": [_sz, C.c_int, _szp],
+    "b200compBitPackCompress": [_vp, _sz, C.c_int, _vp, _vp, _vp, _sz, _vp, _vp, _vp],
     "b200compCompConfigStatus": [_vp],
     "b200compDecompConfigStatus": [_vp],
 }

@@ -69,6 +69,26 @@ hipcompStatus_t b200compDecompConfigStatus(const b200compDecompConfig* cfg);
 void b200compCompConfigDestroy(b200compCompConfig* cfg);
 void b200compDecompConfigDestroy(b200compDecompConfig* cfg);
 
+/* ---- C view of the device-wide primitives (primitives.hpp: RunLengthEncodeGPU, DeltaGPU,
+ * BitPackGPU; reference src/RunLengthEncodeGPU.h, DeltaGPU.h, BitPackGPU.h).  Argument
+ * meaning is that of the C++ static methods; exceptions become hipcompErrorInvalidValue. */
+hipcompStatus_t b200compRleRequiredWorkspaceSize(size_t num, hipcompType_t value_type, hipcompType_t count_type,
+                                                 size_t* bytes);
+hipcompStatus_t b200compRleCompress(void* workspace, size_t workspace_bytes, hipcompType_t value_type,
+                                    void* out_values, hipcompType_t count_type, void* out_counts,
+                                    size_t* num_out_device, const void* in, size_t num, hipStream_t stream);
+hipcompStatus_t b200compRleCompressDownstream(void* workspace, size_t workspace_bytes, hipcompType_t value_type,
+                                              void** out_values_ptr, hipcompType_t count_type,
+                                              void** out_counts_ptr, size_t* num_out_device, const void* in,
+                                              const size_t* num_device, size_t max_num, hipStream_t stream);
+hipcompStatus_t b200compDeltaCompress(hipcompType_t value_type, void** out_values_ptr, const void* in,
+                                      const size_t* num_device, size_t max_num, hipStream_t stream);
+hipcompStatus_t b200compBitPackRequiredWorkspaceSize(size_t num, hipcompType_t type, size_t* bytes);
+hipcompStatus_t b200compBitPackCompress(void* workspace, size_t workspace_bytes, hipcompType_t in_type,
+                                        void* const* out_ptr, const void* in, const size_t* num_device,
+                                        size_t max_num, void* const* min_value_device_ptr,
+                                        unsigned char* const* num_bits_device_ptr, hipStream_t stream);
+
 /* "major.minor.patch (sm_100a)" */
 const char* b200compVersionString(void);
 
