@@ -177,7 +177,7 @@ def test_bitpack_var_bits(vt, bits):
     rng = np.random.default_rng(bits * 8 + width)
     info = np.iinfo(vt)
     span = (1 << bits) - 1
-    lo = info.min if bits == width else int(rng.integers(info.min, info.max - span, endpoint=True))
+    lo = info.min if bits == width else info.min + int(rng.integers(0, 1 << 62)) % (info.max - span - info.min + 1)
     r = rng.integers(0, span, n, dtype=np.uint64, endpoint=True)
     r[0], r[-1] = 0, span  # the range is exactly `bits` wide
     a = (r.astype(np.dtype(vt).str.replace("i", "u")) + np.array(lo, vt).astype(np.dtype(vt).str.replace("i", "u"))).view(vt) \
