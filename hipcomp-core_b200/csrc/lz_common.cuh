@@ -253,11 +253,12 @@ __device__ __forceinline__ void execute_round(uint8_t* out, const uint8_t* comp,
   const uint32_t lane = (uint32_t)lane_id();
   const unsigned le_mask = 0xFFFFFFFFu >> (31u - lane); // bits 0..lane
   uint32_t b = begin, carry = 0;
-  // Round without internal dependencies (every match source ends below `begin`, the
-  // common case for text whose matches reach kilobytes back) and without long runs:
-  // steps need no ordering, so two of them are in flight per iteration and their
-  // loads overlap.
-  const bool far = seq_end == lit_end || (lit_end - off) + (seq_end - lit_end) <= begin;
+  // Round whose matches all reach at least 64 bytes back and that has no long runs: an
+  // iteration produces 64 consecutive bytes, so every match byte it needs lies below the
+  // iteration's first byte, i.e. was stored by an earlier iteration (made visible by the
+  // __syncwarp() that ends each one) or an earlier round.  Two 32-byte steps are in
+  // flight per iteration and their loads overlap.
+  const bool far = seq_end == lit_end || off >= 64u;
   const bool plain = far && (seq_end - pos) < kLongRun;
   if (__all_sync(kFull, plain)) {
     while (b < end) {
@@ -281,8 +282,8 @@ __device__ __forceinline__ void execute_round(uint8_t* out, const uint8_t* comp,
       if (p1 < end) out[p1] = v1;
       carry = c1 + (uint32_t)__popc(s1);
       b += 64u;
+      __syncwarp();
     }
-    __syncwarp();
     return;
   }
   while (b < end) {
