@@ -53,9 +53,10 @@ inline void allow_smem(K kernel, int bytes)
 int group_lanes_from_env(const char* name);
 
 // LZ4 / Snappy decoder variant knob (B200COMP_{LZ4,SNAPPY}_DEC_G): unset -> default,
-// (= "round", the fastest measured), "pipe" -> decoupled parse/exec pipeline, "round" -> one-warp round decoder,
+// (LZ4: "win", the window decoder; Snappy: "round"), "pipe" -> decoupled parse/exec pipeline, "round" -> one-warp
+// round decoder, "win" -> window decoder (shared-memory staged token walk),
 // 4/8/16/32 -> v2 sub-warp group decoder of that width.
-enum : int { kDecoderDefault = -1, kDecoderPipeline = 1, kDecoderRound = 0 };
+enum : int { kDecoderDefault = -1, kDecoderPipeline = 1, kDecoderRound = 0, kDecoderWindow = 2 };
 int decoder_variant_from_env(const char* name);
 
 inline size_t round_up_sz(size_t x, size_t a) { return (x + a - 1) / a * a; }

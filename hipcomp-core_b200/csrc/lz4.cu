@@ -399,6 +399,215 @@ decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, 
   }
 }
 
+// v5 decoder ("window" decoder).  The v3 round decoder spends ~65 warp instructions per
+// sequence walking the token chain (every lane repeats the walk).  Here the chain is
+// reduced to its minimum: a round stages 512 compressed bytes in shared memory (one
+// 16-byte load per lane) and, from the same registers, computes for EVERY byte position
+// the distance to the next token if a token started there (4 positions per SIMD word
+// operation).  The serial part is then "idx += step[idx]", one shared-memory byte load
+// per sequence.  Tokens with extended lengths (a 0xF nibble), the last token of the
+// stream and tokens that cross the window end take a generic path that reads the same
+// window; a sequence whose header does not fit a fresh window (literal runs of hundreds
+// of bytes) is run straight from global memory with vector copies.  After the walk lane
+// k decodes sequence k on its own, and the round executor (lz_common.cuh) produces the
+// output 64 bytes per iteration.
+constexpr int kWin = 512;
+
+struct SlowRec {
+  uint32_t lit_off, nlit, mlen, off;
+};
+
+__global__ void __launch_bounds__(kDecWarps * 32)
+decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
+                         void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
+{
+  __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin];
+  __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
+  __shared__ SlowRec s_rec[kDecWarps][32];
+  const uint32_t lane = (uint32_t)lane_id();
+  const int warp = threadIdx.x >> 5;
+  uint8_t* win = s_win[warp];
+  uint8_t* step = s_step[warp];
+  SlowRec* rec = s_rec[warp];
+  const size_t stride = (size_t)gridDim.x * kDecWarps;
+  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + warp; chunk < batch; chunk += stride) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    const size_t cap64 = out_caps[chunk];
+    const uint32_t cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
+    const uintptr_t cbase = reinterpret_cast<uintptr_t>(comp);
+    uint32_t ci = 0, di = 0;
+    bool ok = true;
+    while (ok && ci < comp_len) {
+      // ---- stage [ci - shift, ci - shift + 512): 16-byte aligned blocks that intersect the stream
+      const uint32_t shift = (uint32_t)((cbase + ci) & 15);
+      const uint32_t wpos = ci - shift; // stream position of window byte 0 (may "underflow" by < 16 at ci = 0)
+      const uint32_t wvalid = min((uint32_t)kWin, comp_len - wpos);
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (16u * lane < wvalid) v = __ldg(reinterpret_cast<const uint4*>(cbase + ci - shift) + lane);
+      *reinterpret_cast<uint4*>(win + 16 * lane) = v;
+      {
+        // step[p] = 3 + (literal nibble) for a plain token at p, 0 when a nibble is 0xF
+        uint4 st;
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t r[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t nl = (w[j] >> 4) & 0x0f0f0f0fu, mc = w[j] & 0x0f0f0f0fu;
+          const uint32_t f = (((nl + 0x01010101u) | (mc + 0x01010101u)) >> 4) & 0x01010101u;
+          r[j] = (nl + 0x03030303u) & ~(f * 0xffu);
+        }
+        st = make_uint4(r[0], r[1], r[2], r[3]);
+        *reinterpret_cast<uint4*>(step + 16 * lane) = st;
+      }
+      __syncwarp();
+      const bool at_stream_end = wpos + wvalid == comp_len;
+
+      // ---- walk the token chain
+      uint32_t idx = shift, k = 0, my_idx = 0;
+      bool my_slow = false, giant = false;
+      while (k < 32u && idx < wvalid) {
+        const uint32_t s = step[idx];
+        if (s != 0u && idx + s <= wvalid) {
+          if (lane == k) my_idx = idx;
+          idx += s;
+          ++k;
+          continue;
+        }
+        // generic parse of the sequence at idx, from the window
+        bool more = false; // header or literals reach past the window
+        uint32_t p = idx;
+        const uint32_t tok = win[p++];
+        uint32_t nlit = tok >> 4, mlen = 0, off = 0;
+        if (nlit == 15u) {
+          uint32_t b = 0xff;
+          while (b == 0xffu) {
+            if (p >= wvalid) { more = true; break; }
+            if (nlit > 0x7FFFFFFFu) { ok = false; break; }
+            b = win[p++];
+            nlit += b;
+          }
+        }
+        if (!ok) break;
+        uint32_t lit_off = p;
+        if (!more) {
+          const uint32_t left = comp_len - (wpos + p); // stream bytes from the first literal on
+          if (nlit > left) { ok = false; break; }
+          if (nlit == left) {
+            // last sequence of the stream: literals only
+            if (p + nlit > wvalid) more = true;
+            else p += nlit;
+          } else {
+            if (nlit + 2u > left) { ok = false; break; }
+            if (p + nlit + 2u > wvalid) more = true;
+            else {
+              off = (uint32_t)win[p + nlit] | ((uint32_t)win[p + nlit + 1] << 8);
+              p += nlit + 2u;
+              mlen = 4u + (tok & 15u);
+              if ((tok & 15u) == 15u) {
+                uint32_t b = 0xff;
+                while (b == 0xffu) {
+                  if (p >= wvalid) { more = true; break; }
+                  if (mlen > 0x7FFFFFFFu) { ok = false; break; }
+                  b = win[p++];
+                  mlen += b;
+                }
+              }
+              if (!ok) break;
+              if (!more && off == 0u) { ok = false; break; }
+            }
+          }
+        }
+        if (more) {
+          if (at_stream_end) {
+            // the window already holds the rest of the stream: the header is truncated
+            // (literal runs that pass the end were diagnosed above)
+            if (!(k == 0u && idx == shift)) break; // re-stage at this token first: cheap and uniform
+            ok = false;
+            break;
+          }
+          if (k == 0u && idx == shift) giant = true;
+          break;
+        }
+        if (lane == k) {
+          my_idx = idx;
+          my_slow = true;
+          rec[k] = SlowRec{lit_off, nlit, mlen, off};
+        }
+        idx = p;
+        ++k;
+      }
+      if (!ok) break;
+      if (giant) {
+        // one sequence straight from global memory (long literal run and / or long headers)
+        const uint32_t tok = __ldg(comp + ci);
+        ++ci;
+        uint32_t nlit = tok >> 4;
+        if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
+        if (nlit > comp_len - ci || nlit > cap - di) { ok = false; break; }
+        group_copy_ro<32>(out + di, comp + ci, nlit, lane);
+        ci += nlit;
+        di += nlit;
+        if (ci < comp_len) {
+          if (ci + 2 > comp_len) { ok = false; break; }
+          const uint32_t off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
+          ci += 2;
+          uint32_t mlen = 4 + (tok & 15);
+          if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
+          if (off == 0 || off > di || mlen > cap - di) { ok = false; break; }
+          __syncwarp();
+          group_copy_match<32>(out + di, off, mlen, lane, kFull);
+          di += mlen;
+        }
+        __syncwarp();
+        continue;
+      }
+      if (k == 0u) {
+        // at_stream_end with a truncated header after a re-stage lands here as k == 0 && idx == shift
+        ok = false;
+        break;
+      }
+      // ---- lane j decodes sequence j
+      __syncwarp();
+      uint32_t my_nlit = 0, my_mlen = 0, my_off = 0, my_lp = 0;
+      if (lane < k) {
+        if (my_slow) {
+          const SlowRec r = rec[lane];
+          my_nlit = r.nlit;
+          my_mlen = r.mlen;
+          my_off = r.off;
+          my_lp = wpos + r.lit_off;
+        } else {
+          const uint32_t tok = win[my_idx];
+          my_nlit = tok >> 4;
+          my_mlen = 4u + (tok & 15u);
+          const uint32_t op = my_idx + 1u + my_nlit;
+          my_off = (uint32_t)win[op] | ((uint32_t)win[op + 1u] << 8);
+          my_lp = wpos + my_idx + 1u;
+        }
+      }
+      const bool zero_off = lane < k && my_mlen != 0u && my_off == 0u;
+      uint32_t total;
+      const uint32_t pos = add_sat_u32(di, warp_excl_sum_sat(add_sat_u32(my_nlit, my_mlen), total));
+      const uint32_t lit_end = add_sat_u32(pos, my_nlit);
+      const uint32_t seq_end = add_sat_u32(lit_end, my_mlen);
+      const bool bad = zero_off || seq_end > cap || (my_mlen != 0 && my_off > lit_end);
+      if (__any_sync(kFull, bad)) { ok = false; break; }
+      const uint32_t end = di + total;
+      execute_round(out, comp, di, end, pos, lit_end, seq_end, my_lp - pos, my_off);
+      di = end;
+      ci = wpos + idx;
+      __syncwarp(); // the window is rewritten next
+    }
+    if (lane == 0) {
+      if (actual) actual[chunk] = ok ? di : 0;
+      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
+    }
+    __syncwarp();
+  }
+}
+
 // Lanes per chunk: narrow groups when the batch has enough chunks to fill the
 // machine with them, the whole warp for small batches.  B200COMP_LZ4_DEC_G overrides.
 // v4 decoder (lz_pipeline.cuh): LZ4 token walk for one parse lane.
@@ -617,7 +826,15 @@ hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compr
         device_actual_uncompressed_bytes, device_statuses, batch_size);
     return check_launch(fn);
   }
-  if (variant == kDecoderDefault || variant == kDecoderRound) {
+  if (variant == kDecoderDefault || variant == kDecoderWindow) {
+    const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
+    const size_t cap = (size_t)sm_count() * 16;
+    lz4::decompress_window_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
+        device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
+        device_actual_uncompressed_bytes, device_statuses, batch_size);
+    return check_launch(fn);
+  }
+  if (variant == kDecoderRound) {
     const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
     const size_t cap = (size_t)sm_count() * 16;
     lz4::decompress_round_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(

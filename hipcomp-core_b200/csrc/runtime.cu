@@ -35,6 +35,7 @@ int decoder_variant_from_env(const char* name)
   if (!v || !*v) return kDecoderDefault;
   if (std::strcmp(v, "pipe") == 0) return kDecoderPipeline;
   if (std::strcmp(v, "round") == 0) return kDecoderRound;
+  if (std::strcmp(v, "win") == 0) return kDecoderWindow;
   const int g = std::atoi(v);
   return (g == 4 || g == 8 || g == 16 || g == 32) ? g : kDecoderDefault;
 }
