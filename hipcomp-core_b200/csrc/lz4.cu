@@ -12,6 +12,8 @@
 #include "lz_common.cuh"
 #include "lz_pipeline.cuh"
 
+#include <cstdlib>
+
 #pragma GCC visibility push(default)
 #include "hipcomp/lz4.h"
 #pragma GCC visibility pop
@@ -78,8 +80,11 @@ constexpr int kCompWarps = 4;
 // every valid lane before the intra-window twin search finishes -> candidate verify
 // -> word-wide match extension.  Literals that lie inside the current window are
 // stored straight from the key registers.
+#ifndef B200_LZ4_COMP_MINB
+#define B200_LZ4_COMP_MINB 10
+#endif
 template <int TS, bool kGlobalTable>
-__global__ void __launch_bounds__(kCompWarps * 32)
+__global__ void __launch_bounds__(kCompWarps * 32, B200_LZ4_COMP_MINB)
 compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
                 size_t batch, uint32_t ht_size, uint16_t* gtables)
 {
@@ -96,7 +101,10 @@ compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const*
     uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
     const uint32_t length = (uint32_t)in_bytes[chunk];
     const uint32_t typed_length = (length + TS - 1) / TS;
-    uint16_t* table = kGlobalTable ? gtables + chunk * ht_size : stables + (size_t)warp * ht_size;
+    // global tables belong to the (persistent) warp, not to the chunk: the set of live tables is
+    // gridDim.x * kCompWarps * 2 * ht_size bytes, sized by the launcher to stay inside the L2
+    uint16_t* table = kGlobalTable ? gtables + ((size_t)blockIdx.x * kCompWarps + warp) * ht_size
+                                   : stables + (size_t)warp * ht_size;
 
     if (ht_size >= 8 && ((reinterpret_cast<uintptr_t>(table) & 15) == 0)) {
       uint4* t128 = reinterpret_cast<uint4*>(table);
@@ -762,7 +770,14 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
     return fail(hipcompErrorInvalidValue, fn, "'device_temp_ptr' must not be null.");
   const int smem = global_table ? 0 : (int)(ht * sizeof(uint16_t) * lz4::kCompWarps);
   const size_t need = (batch_size + lz4::kCompWarps - 1) / lz4::kCompWarps;
-  const size_t cap = (size_t)sm_count() * 16;
+  // CTAs per SM: with global tables, few enough that every live table stays L2-resident
+  // (B200COMP_LZ4_COMP_CTAS overrides; the workspace always has room: grid * kCompWarps <= batch)
+  static const int env_ctas = [] {
+    const char* v = std::getenv("B200COMP_LZ4_COMP_CTAS");
+    return v ? std::atoi(v) : 0;
+  }();
+  const int ctas_per_sm = env_ctas > 0 ? env_ctas : (global_table ? B200_LZ4_COMP_MINB : 16);
+  const size_t cap = (size_t)sm_count() * ctas_per_sm;
   const int grid = (int)(need < cap ? need : cap);
   uint16_t* gt = static_cast<uint16_t*>(device_temp_ptr);
 #define B200_LZ4_LAUNCH(TS)                                                                                        \
