@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(kDecWarps * 32)
 decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
                          void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
 {
-  __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin];
+  __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin + 32]; // walk may peek <= 18 bytes past the window
   __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
   __shared__ SlowRec s_rec[kDecWarps][32];
   const uint32_t lane = (uint32_t)lane_id();
@@ -456,15 +456,17 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       if (16u * lane < wvalid) v = __ldg(reinterpret_cast<const uint4*>(cbase + ci - shift) + lane);
       *reinterpret_cast<uint4*>(win + 16 * lane) = v;
       {
-        // step[p] = 3 + (literal nibble) for a plain token at p, 0 when a nibble is 0xF
+        // step[p], for a token at p: 3 + literal nibble (token, literals, offset); bit 7 set when the
+        // match nibble is 0xF (a length byte follows the offset); 0 when the literal nibble is 0xF
         uint4 st;
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
         uint32_t r[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const uint32_t nl = (w[j] >> 4) & 0x0f0f0f0fu, mc = w[j] & 0x0f0f0f0fu;
-          const uint32_t f = (((nl + 0x01010101u) | (mc + 0x01010101u)) >> 4) & 0x01010101u;
-          r[j] = (nl + 0x03030303u) & ~(f * 0xffu);
+          const uint32_t nl15 = ((nl + 0x01010101u) >> 4) & 0x01010101u;
+          const uint32_t mc15 = ((mc + 0x01010101u) << 3) & 0x80808080u;
+          r[j] = ((nl + 0x03030303u) | mc15) & ~(nl15 * 0xffu);
         }
         st = make_uint4(r[0], r[1], r[2], r[3]);
         *reinterpret_cast<uint4*>(step + 16 * lane) = st;
@@ -477,9 +479,15 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       bool my_slow = false, giant = false;
       while (k < 32u && idx < wvalid) {
         const uint32_t s = step[idx];
-        if (s != 0u && idx + s <= wvalid) {
+        uint32_t adv = s & 0x7fu;
+        if (s & 0x80u) {
+          // match length 19..273: exactly one length byte unless it reads 0xFF
+          const uint32_t e = win[idx + adv];
+          adv = e == 0xffu ? 0u : adv + 1u;
+        }
+        if (adv != 0u && idx + adv <= wvalid) {
           if (lane == k) my_idx = idx;
-          idx += s;
+          idx += adv;
           ++k;
           continue;
         }
@@ -592,6 +600,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
           my_mlen = 4u + (tok & 15u);
           const uint32_t op = my_idx + 1u + my_nlit;
           my_off = (uint32_t)win[op] | ((uint32_t)win[op + 1u] << 8);
+          if ((tok & 15u) == 15u) my_mlen += win[op + 2u];
           my_lp = wpos + my_idx + 1u;
         }
       }
