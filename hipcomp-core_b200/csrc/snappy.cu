@@ -416,6 +416,180 @@ decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, 
   }
 }
 
+// v5 decoder ("window" decoder, same scheme as lz4::decompress_window_kernel).  A round stages
+// 512 compressed bytes in shared memory and computes, for every byte position, how far the next
+// element starts if an element started there (tag kinds folded with SIMD-in-word arithmetic), so
+// the serial walk is one shared-memory byte load per element.  Lane k then decodes element k from
+// the window; validation (offset within the output so far, length within the bytes left) runs in
+// parallel over the round after a prefix sum, and an invalid element cuts the round in front of
+// it: the elements before it are still produced, as the sequential decoder does.  Literals with
+// an extended length (>= 61 bytes) and elements that do not fit a fresh window run one at a time
+// from global memory with vector copies.
+constexpr int kWin = 512;
+
+__global__ void __launch_bounds__(kDecWarps * 32)
+decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
+                         void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
+{
+  __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin + 32];
+  __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
+  const uint32_t lane = (uint32_t)lane_id();
+  const int warp = threadIdx.x >> 5;
+  uint8_t* win = s_win[warp];
+  uint8_t* step = s_step[warp];
+  const size_t stride = (size_t)gridDim.x * kDecWarps;
+  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + warp; chunk < batch; chunk += stride) {
+    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
+    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
+    const size_t cap64 = out_caps[chunk];
+    const uintptr_t cbase = reinterpret_cast<uintptr_t>(comp);
+    uint32_t size = 0, cur = 0, left = 0;
+    bool ok = comp_len != 0 && comp != nullptr;
+    if (ok) ok = read_preamble(comp, comp_len, cur, size);
+    if (ok) {
+      const size_t cap = cap64 == 0 ? size : cap64;
+      if ((cur >= comp_len && size != 0) || size > cap) ok = false;
+    }
+    if (!ok) size = 0;
+    left = size;
+    uint32_t dst = 0;
+    while (ok && left > 0) {
+      if (cur >= comp_len) { ok = false; break; }
+      // ---- stage the window
+      const uint32_t shift = (uint32_t)((cbase + cur) & 15);
+      const uint32_t wpos = cur - shift;
+      const uint32_t wvalid = min((uint32_t)kWin, comp_len - wpos);
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (16u * lane < wvalid) v = __ldg(reinterpret_cast<const uint4*>(cbase + cur - shift) + lane);
+      *reinterpret_cast<uint4*>(win + 16 * lane) = v;
+      {
+        // step[p] for a tag at p: literal of 1..60 bytes -> 1 + length; copy kinds 1/2/3 -> 2/3/5;
+        // 0 for a literal with an extended length
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t r[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t k1 = w[j] & 0x01010101u, k2 = (w[j] >> 1) & 0x01010101u;
+          const uint32_t len6 = (w[j] >> 2) & 0x3f3f3f3fu;
+          const uint32_t is_copy = (k1 | k2) * 0xffu;
+          const uint32_t ext = ((len6 + 0x04040404u) >> 6) & 0x01010101u; // len6 >= 60
+          const uint32_t lit_step = (len6 + 0x02020202u) & ~(ext * 0xffu);
+          const uint32_t copy_step = 0x01010101u + k1 + 2u * k2 + (k1 & k2);
+          r[j] = (copy_step & is_copy) | (lit_step & ~is_copy);
+        }
+        *reinterpret_cast<uint4*>(step + 16 * lane) = make_uint4(r[0], r[1], r[2], r[3]);
+      }
+      __syncwarp();
+
+      // ---- walk the element chain
+      uint32_t idx = shift, k = 0, my_idx = 0;
+      while (k < 32u && idx < wvalid) {
+        const uint32_t s = step[idx];
+        if (s == 0u || idx + s > wvalid) break;
+        if (lane == k) my_idx = idx;
+        idx += s;
+        ++k;
+      }
+      if (k == 0u) {
+        // one element straight from global memory: extended literal, or an element cut by the window end
+        uint32_t blen, offset = 0;
+        const uint32_t b0 = __ldg(comp + cur);
+        if (b0 & 3) {
+          if ((b0 & 3) == 1) {
+            if (cur + 2 > comp_len) { ok = false; break; }
+            offset = ((b0 & 0xe0) << 3) | __ldg(comp + cur + 1);
+            blen = ((b0 >> 2) & 7) + 4;
+            cur += 2;
+          } else if ((b0 & 3) == 2) {
+            if (cur + 3 > comp_len) { ok = false; break; }
+            offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8);
+            blen = (b0 >> 2) + 1;
+            cur += 3;
+          } else {
+            if (cur + 5 > comp_len) { ok = false; break; }
+            offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8)
+                     | ((uint32_t)__ldg(comp + cur + 3) << 16) | ((uint32_t)__ldg(comp + cur + 4) << 24);
+            blen = (b0 >> 2) + 1;
+            cur += 5;
+          }
+          if (offset == 0 || offset > dst || left < blen) { ok = false; break; }
+          __syncwarp();
+          group_copy_match<32>(out + dst, offset, blen, lane, kFull);
+        } else {
+          blen = b0 >> 2;
+          cur += 1;
+          if (blen >= 60) {
+            const uint32_t nb = blen - 59;
+            if (cur + nb > comp_len) { ok = false; break; }
+            blen = 0;
+            for (uint32_t i = 0; i < nb; ++i) blen |= (uint32_t)__ldg(comp + cur + i) << (8 * i);
+            cur += nb;
+          }
+          if (blen == 0xffffffffu) { ok = false; break; }
+          blen += 1;
+          if (left < blen || blen > comp_len - cur) { ok = false; break; }
+          group_copy_ro<32>(out + dst, comp + cur, blen, lane);
+          cur += blen;
+        }
+        dst += blen;
+        left -= blen;
+        __syncwarp();
+        continue;
+      }
+      // ---- lane j decodes element j
+      uint32_t my_len = 0, my_off = 0, my_lp = 0; // my_off == 0: literal
+      bool zero_off = false;
+      if (lane < k) {
+        const uint32_t tag = win[my_idx], kind = tag & 3u;
+        if (kind == 0u) {
+          my_len = (tag >> 2) + 1u;
+          my_lp = wpos + my_idx + 1u;
+        } else {
+          if (kind == 1u) {
+            my_off = ((tag & 0xe0u) << 3) | win[my_idx + 1u];
+            my_len = ((tag >> 2) & 7u) + 4u;
+          } else {
+            my_off = (uint32_t)win[my_idx + 1u] | ((uint32_t)win[my_idx + 2u] << 8);
+            if (kind == 3u) my_off |= ((uint32_t)win[my_idx + 3u] << 16) | ((uint32_t)win[my_idx + 4u] << 24);
+            my_len = (tag >> 2) + 1u;
+          }
+          zero_off = my_off == 0u;
+        }
+      }
+      // ---- validate in stream order: an element must fit the bytes left and a copy must start
+      //      inside the output produced so far; elements past the end of the output are ignored
+      uint32_t total;
+      const uint32_t rel = warp_excl_sum_sat(my_len, total);
+      const bool past_end = lane < k && rel >= left;            // output already complete before this element
+      const bool bad = lane < k && !past_end && (my_len > left - rel || zero_off || my_off > dst + rel);
+      const unsigned stop = __ballot_sync(kFull, bad || past_end || lane >= k);
+      const uint32_t nrun = stop ? (uint32_t)__ffs((int)stop) - 1u : 32u; // elements that run
+      const unsigned bad_mask = __ballot_sync(kFull, bad);
+      const bool failed = nrun < 32u && ((bad_mask >> nrun) & 1u);
+      if (lane >= nrun) my_len = 0;
+      const uint32_t run_total = __shfl_sync(kFull, rel, (int)(nrun & 31u)) ;
+      const uint32_t produced = nrun == 32u ? total : run_total;
+      const uint32_t pos = dst + rel;
+      const uint32_t seq_end = pos + my_len;
+      const uint32_t lit_end = my_off == 0 ? seq_end : pos;
+      execute_round(out, comp, dst, dst + produced, pos, lit_end, seq_end, my_lp - pos, my_off);
+      dst += produced;
+      left -= produced;
+      if (failed) { ok = false; break; }
+      // stream position after the last element that ran
+      const uint32_t nidx = __shfl_sync(kFull, my_idx, (int)(nrun & 31u));
+      cur = wpos + (nrun == k ? idx : nidx);
+      __syncwarp();
+    }
+    if (lane == 0) {
+      if (actual) actual[chunk] = size - left;
+      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
+    }
+    __syncwarp();
+  }
+}
+
 // v4 decoder (lz_pipeline.cuh): Snappy element walk for one parse lane.
 struct PipeCodec {
   struct State {
@@ -575,7 +749,15 @@ hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_co
             device_actual_uncompressed_bytes, device_statuses, batch_size);
     return check_launch(fn);
   }
-  if (variant == kDecoderDefault || variant == kDecoderRound) {
+  if (variant == kDecoderDefault || variant == kDecoderWindow) {
+    const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
+    const size_t cap = (size_t)sm_count() * 16;
+    snappy::decompress_window_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
+        device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
+        device_actual_uncompressed_bytes, device_statuses, batch_size);
+    return check_launch(fn);
+  }
+  if (variant == kDecoderRound) {
     const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
     const size_t cap = (size_t)sm_count() * 16;
     snappy::decompress_round_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
