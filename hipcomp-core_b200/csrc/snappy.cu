@@ -11,6 +11,8 @@
 #include "lz_common.cuh"
 #include "lz_pipeline.cuh"
 
+#include <cstdlib>
+
 #pragma GCC visibility push(default)
 #include "hipcomp/snappy.h"
 #pragma GCC visibility pop
@@ -67,18 +69,22 @@ __device__ __forceinline__ uint32_t put_copy(uint8_t* dst, uint32_t o, uint32_t 
   return o + 3;
 }
 
-__global__ void __launch_bounds__(kCompWarps * 32)
+// One warp per chunk, an 8 KiB hash map per warp in (dynamic) shared memory.  WARPS = warps per CTA:
+// 4 (six CTAs per SM) or 28 (one CTA per SM, 224 KiB of maps): the launcher takes the shape that
+// needs fewer waves over the batch, e.g. 4096 chunks (C1) fit 148 x 28 = 4144 warps in one wave.
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, WARPS == 4 ? 6 : 1)
 compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
                 size_t batch)
 {
-  __shared__ uint16_t maps[kCompWarps][1 << kHashBits];
+  extern __shared__ __align__(16) uint16_t maps[];
   const uint32_t lane = (uint32_t)lane_id();
   const int warp = threadIdx.x >> 5;
-  uint16_t* map = maps[warp];
+  uint16_t* map = maps + (size_t)warp * (1 << kHashBits);
   const unsigned lt = lanemask_lt();
-  const size_t stride = (size_t)gridDim.x * kCompWarps;
+  const size_t stride = (size_t)gridDim.x * WARPS;
 
-  for (size_t chunk = (size_t)blockIdx.x * kCompWarps + warp; chunk < batch; chunk += stride) {
+  for (size_t chunk = (size_t)blockIdx.x * WARPS + warp; chunk < batch; chunk += stride) {
     const uint8_t* src = static_cast<const uint8_t*>(in_ptrs[chunk]);
     uint8_t* dst = static_cast<uint8_t*>(out_ptrs[chunk]);
     const uint32_t len = (uint32_t)in_bytes[chunk];
@@ -811,10 +817,25 @@ hipcompStatus_t hipcompBatchedSnappyCompressAsync(const void* const* device_unco
   B200_CHECK_NOT_NULL(device_compressed_ptr, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   if (batch_size == 0) return hipcompSuccess;
-  const size_t need = (batch_size + snappy::kCompWarps - 1) / snappy::kCompWarps;
-  const size_t cap = (size_t)sm_count() * 6;
-  snappy::compress_kernel<<<(int)(need < cap ? need : cap), snappy::kCompWarps * 32, 0, stream>>>(
-      device_uncompressed_ptr, device_uncompressed_bytes, device_compressed_ptr, device_compressed_bytes, batch_size);
+  const size_t sms = (size_t)sm_count();
+  constexpr size_t kMapBytes = sizeof(uint16_t) << snappy::kHashBits;
+  // waves over the batch: 24 warps per SM as 6 CTAs of 4, or 28 as one CTA
+  const size_t waves4 = (batch_size + sms * 24 - 1) / (sms * 24), waves28 = (batch_size + sms * 28 - 1) / (sms * 28);
+  static const int forced = [] { const char* v = std::getenv("B200COMP_SNAPPY_COMP_WARPS"); return v ? std::atoi(v) : 0; }();
+  const bool big = forced ? forced == 28 : waves28 < waves4;
+  if (big) {
+    constexpr int W = 28;
+    allow_smem(snappy::compress_kernel<W>, (int)(W * kMapBytes));
+    const size_t need = (batch_size + W - 1) / W;
+    snappy::compress_kernel<W><<<(int)(need < sms ? need : sms), W * 32, W * kMapBytes, stream>>>(
+        device_uncompressed_ptr, device_uncompressed_bytes, device_compressed_ptr, device_compressed_bytes, batch_size);
+  } else {
+    constexpr int W = snappy::kCompWarps;
+    const size_t need = (batch_size + W - 1) / W;
+    const size_t cap = sms * 6;
+    snappy::compress_kernel<W><<<(int)(need < cap ? need : cap), W * 32, W * kMapBytes, stream>>>(
+        device_uncompressed_ptr, device_uncompressed_bytes, device_compressed_ptr, device_compressed_bytes, batch_size);
+  }
   return check_launch(fn);
 }
 
