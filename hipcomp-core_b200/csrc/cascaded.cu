@@ -624,6 +624,123 @@ __device__ void raw_copy(const T* in, size_t n, uint8_t* out)
   if (lane < (int)(padded - bytes)) dst[bytes + lane] = 0;
 }
 
+// Fused fast path for the headline option set (num_RLEs = 1, num_deltas = 1, 4-byte elements, full
+// 4096-byte chunk, 16-byte aligned source).  Same bytes as the generic layer loop, different data
+// movement: the chunk never sits in shared memory.  Each lane keeps 8 coalesced 16-byte vectors
+// (elements 128k + 4*lane + j) in registers, run-end flags come from register compares plus one
+// rotating shuffle per vector, the 8 per-tile flag counts are scanned as two byte-packed words, and
+// only the compacted (run value, run end) pairs go to shared memory.  One striped pass then turns
+// ends into lengths and values into deltas, in place, in the swizzled layout write_array packs from.
+// Returns false when the chunk does not fit (caller falls back to the raw partition).
+template <typename T>
+__device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, size_t limit, bool use_bp, T* A,
+                                    uint16_t* C)
+{
+  static_assert(sizeof(T) == 4, "fast path is for 4-byte elements");
+  constexpr int N = kChunkBytes / 4;
+  const int lane = lane_id();
+  const size_t chunk_start = cur;
+  cur += 16; // meta_size(4, 1, 1)
+  if (cur > limit) return false;
+
+  uint4 v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = ld_stream16(reinterpret_cast<const uint4*>(src) + lane + 32 * k);
+
+  // run-end flags, 4 per vector
+  uint32_t fl[8];
+  uint32_t p0 = 0, p1 = 0; // per-tile flag counts, one byte per tile
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t z = (lane == 0 && k < 7) ? v[k < 7 ? k + 1 : k].x : v[k].x;
+    const uint32_t nx = __shfl_sync(kFull, z, (lane + 1) & 31);
+    uint32_t f = (v[k].x != v[k].y ? 1u : 0u) | (v[k].y != v[k].z ? 2u : 0u) | (v[k].z != v[k].w ? 4u : 0u) |
+                 (v[k].w != nx ? 8u : 0u);
+    if (k == 7 && lane == 31) f |= 8u; // last element of the chunk ends a run
+    fl[k] = f;
+    const uint32_t c = (uint32_t)__popc(f);
+    if (k < 4) p0 |= c << (8 * k);
+    else p1 |= c << (8 * (k - 4));
+  }
+  // inclusive scan over lanes of the byte-packed counts (a tile holds <= 128 flags: no carry between bytes)
+  uint32_t s0 = p0, s1 = p1;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o0 = __shfl_up_sync(kFull, s0, d);
+    const uint32_t o1 = __shfl_up_sync(kFull, s1, d);
+    if (lane >= d) {
+      s0 += o0;
+      s1 += o1;
+    }
+  }
+  const uint32_t t0 = __shfl_sync(kFull, s0, 31), t1 = __shfl_sync(kFull, s1, 31);
+  const uint32_t x0 = s0 - p0, x1 = s1 - p1; // exclusive, per tile
+  const T seed = (T)__shfl_sync(kFull, v[0].x, 0);
+
+  __syncwarp(); // the previous chunk's packing reads of A / C are complete
+  uint32_t base = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t ex = ((k < 4 ? x0 : x1) >> (8 * (k & 3))) & 0xffu;
+    const uint32_t tt = ((k < 4 ? t0 : t1) >> (8 * (k & 3))) & 0xffu;
+    T* pv = A + base + ex;
+    uint16_t* pe = C + base + ex;
+    const uint32_t e0 = 128u * k + 4u * (uint32_t)lane + 1u; // run end = index + 1
+    const uint32_t f = fl[k];
+    if (f & 1u) { *pv++ = (T)v[k].x; *pe++ = (uint16_t)e0; }
+    if (f & 2u) { *pv++ = (T)v[k].y; *pe++ = (uint16_t)(e0 + 1); }
+    if (f & 4u) { *pv++ = (T)v[k].z; *pe++ = (uint16_t)(e0 + 2); }
+    if (f & 8u) { *pv++ = (T)v[k].w; *pe++ = (uint16_t)(e0 + 3); }
+    base += tt;
+  }
+  const int m = (int)base; // number of runs, >= 1
+  __syncwarp();
+
+  // ends -> lengths, values -> deltas, rewritten in place in swizzled order: the swizzle permutes inside a
+  // 32-element block of A and a 64-element block of C, so one step covers 64 runs (two per lane)
+  uint32_t carry = 0;
+  for (int u = 0; u * 64 < m; ++u) {
+    const int r0 = 64 * u + lane, r1 = r0 + 32;
+    const uint32_t e0 = r0 < m ? (uint32_t)C[r0] : 0u;
+    const uint32_t e1 = r1 < m ? (uint32_t)C[r1] : 0u;
+    const T a0 = r0 < m ? A[r0] : (T)0;
+    const T n0 = r0 + 1 < m ? A[r0 + 1] : (T)0;
+    const T a1 = r1 < m ? A[r1] : (T)0;
+    const T n1 = r1 + 1 < m ? A[r1 + 1] : (T)0;
+    uint32_t q0 = __shfl_up_sync(kFull, e0, 1);
+    uint32_t q1 = __shfl_up_sync(kFull, e1, 1);
+    const uint32_t l0 = __shfl_sync(kFull, e0, 31);
+    if (lane == 0) {
+      q0 = carry;
+      q1 = l0;
+    }
+    carry = __shfl_sync(kFull, e1, 31);
+    __syncwarp();
+    const int sc = (u & 3) << 4; // ((r >> 5) & 7) << 3 for r0; r1 adds 8
+    if (r0 < m) C[r0 ^ sc] = (uint16_t)(e0 - q0);
+    if (r1 < m) C[r1 ^ (sc | 8)] = (uint16_t)(e1 - q1);
+    const int sa = ((2 * u) & 7) << 2;
+    if (r0 + 1 < m) A[r0 ^ sa] = (T)(n0 - a0);
+    if (r1 + 1 < m) A[r1 ^ (sa | 4)] = (T)(n1 - a1);
+  }
+  __syncwarp();
+
+  uint32_t ob_counts, ob_vals;
+  if (!write_array<uint16_t, N>(C, m, out + cur, limit - cur, use_bp, ob_counts)) return false;
+  cur += (ob_counts + 3u) & ~3u;
+  if (!write_array<T, N>(A, m - 1, out + cur, limit - cur, use_bp, ob_vals)) return false;
+  cur += (ob_vals + 3u) & ~3u;
+  if (lane == 0) {
+    uint32_t* mw = reinterpret_cast<uint32_t*>(out + chunk_start);
+    mw[0] = (uint32_t)(cur - chunk_start);
+    mw[1] = ob_counts;
+    mw[2] = ob_vals;
+    mw[3] = (uint32_t)seed;
+  }
+  __syncwarp();
+  return true;
+}
+
 // One warp compresses one partition.  (reference do_cascaded_compression_kernel :761-1058)
 template <typename T>
 __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, size_t* comp_bytes_out, int type_id,
@@ -649,7 +766,15 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
   size_t cur = 8;
   const int layers = R > D ? R : D;
 
+  const bool fast_r1d1 = W == 4 && R == 1 && D == 1 && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
+
   for (size_t c = 0; c < n_chunks && use_compression; ++c) {
+    if constexpr (sizeof(T) == 4) {
+      if (fast_r1d1 && n_total - c * N >= (size_t)N) {
+        if (!compress_chunk_r1d1<T>(in + c * N, out, cur, limit, bp != 0, A, C)) use_compression = false;
+        continue;
+      }
+    }
     const size_t chunk_start = cur;
     cur += msize;
     if (cur > limit) { use_compression = false; break; }

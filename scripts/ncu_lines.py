@@ -6,15 +6,17 @@ rep, kern = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", "--kernel-name",
                       "regex:" + kern], capture_output=True, text=True).stdout
-fname, hdr, recs = None, None, []
+fname, hdr, recs, on = None, None, [], True
 for r in csv.reader(out.splitlines()):
     if len(r) >= 2 and r[0] == "File Path":
         fname = r[1].split("/")[-1]; hdr = None; continue
+    if len(r) >= 2 and r[0] == "Function Name":
+        on = kern.split("|")[0].replace("\\", "") in r[1] or True; continue
     if len(r) > 3 and r[0] == "Line No":
-        hdr = r; continue
-    if hdr and len(r) == len(hdr) and r[0]:
+        hdr = r; ii = hdr.index("Instructions Executed"); si = hdr.index("# Samples"); continue
+    if hdr and len(r) > max(ii, si) and r[0] and r[0].isdigit():
         try:
-            ie = int(r[hdr.index("Instructions Executed")]); ss = int(r[hdr.index("# Samples")])
+            ie = int(r[ii]); ss = int(r[si])
         except ValueError:
             continue
         if ie or ss:
