@@ -29,6 +29,9 @@ namespace cascaded {
 constexpr int kChunkBytes = 4096;
 constexpr int kWarpsPerCta = 4;
 constexpr int kMaxMetaBytes = 64;
+#ifndef B200_CASC_COMP_MINB
+#define B200_CASC_COMP_MINB 5
+#endif
 
 // Swizzled shared-memory array of E.  Element i lives at p(i): the 16-byte vector
 // index is XORed with (i / 32) & 7.  Vectors stay contiguous and aligned.
@@ -271,6 +274,41 @@ __device__ bool write_array(const E* arr, int n, uint8_t* out, size_t avail, boo
         pack32_dispatch<MAXBW>(bw, d, data, g * (int)bw, words);
       }
     }
+  }
+  out_bytes = bytes;
+  return true;
+}
+
+// Bit-packed serialisation when the caller already knows min / max (fused paths): header + blocked
+// packing with no per-element bound checks - the caller has filled arr[n .. roundUp32(n)) with `mn`, so
+// the padding elements pack as zero.  Same bytes as write_array(use_bp = true).  E is 2 or 4 bytes.
+template <typename E>
+__device__ __forceinline__ bool write_packed_known(const E* arr, int n, int32_t mn, int32_t mx, uint8_t* out,
+                                                   size_t avail, uint32_t& out_bytes)
+{
+  static_assert(sizeof(E) == 2 || sizeof(E) == 4, "2- or 4-byte elements");
+  constexpr int VE = Swz<E>::VE;
+  const int lane = lane_id();
+  const uint32_t bw = 32u - (uint32_t)__clz((int)((uint32_t)mx - (uint32_t)mn));
+  const int words = (int)(((uint32_t)n * bw + 31u) >> 5);
+  const uint32_t bytes = 8u + 4u * (uint32_t)words;
+  if (bytes > avail) return false;
+  uint32_t* outw = reinterpret_cast<uint32_t*>(out);
+  const E fr = (E)mn;
+  if (lane == 0) {
+    outw[0] = (uint32_t)fr;
+    outw[1] = (bw << 16) | (uint32_t)n;
+  }
+  const int g = lane;
+  if (bw > 0 && (g << 5) < n) {
+    uint32_t d[32];
+#pragma unroll
+    for (int j = 0; j < 32 / VE; ++j) {
+      const Vec<E> v = ld_vec<E>(arr, (g << 5) + j * VE);
+#pragma unroll
+      for (int c = 0; c < VE; ++c) d[j * VE + c] = (uint32_t)(E)(v.e[c] - fr);
+    }
+    pack32_dispatch<sizeof(E) == 2 ? 16 : 32>(bw, d, outw + 2, g * (int)bw, words);
   }
   out_bytes = bytes;
   return true;
@@ -699,6 +737,7 @@ __device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, siz
   // ends -> lengths, values -> deltas, rewritten in place in swizzled order: the swizzle permutes inside a
   // 32-element block of A and a 64-element block of C, so one step covers 64 runs (two per lane)
   uint32_t carry = 0;
+  int32_t cmn = 0x7fffffff, cmx = (int32_t)0x80000000, vmn = 0x7fffffff, vmx = (int32_t)0x80000000;
   for (int u = 0; u * 64 < m; ++u) {
     const int r0 = 64 * u + lane, r1 = r0 + 32;
     const uint32_t e0 = r0 < m ? (uint32_t)C[r0] : 0u;
@@ -717,19 +756,58 @@ __device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, siz
     carry = __shfl_sync(kFull, e1, 31);
     __syncwarp();
     const int sc = (u & 3) << 4; // ((r >> 5) & 7) << 3 for r0; r1 adds 8
-    if (r0 < m) C[r0 ^ sc] = (uint16_t)(e0 - q0);
-    if (r1 < m) C[r1 ^ (sc | 8)] = (uint16_t)(e1 - q1);
+    const int32_t c0 = (int32_t)(int16_t)(e0 - q0), c1 = (int32_t)(int16_t)(e1 - q1);
+    const int32_t d0 = (int32_t)(n0 - a0), d1 = (int32_t)(n1 - a1);
+    if (r0 < m) {
+      C[r0 ^ sc] = (uint16_t)c0;
+      cmn = min(cmn, c0);
+      cmx = max(cmx, c0);
+    }
+    if (r1 < m) {
+      C[r1 ^ (sc | 8)] = (uint16_t)c1;
+      cmn = min(cmn, c1);
+      cmx = max(cmx, c1);
+    }
     const int sa = ((2 * u) & 7) << 2;
-    if (r0 + 1 < m) A[r0 ^ sa] = (T)(n0 - a0);
-    if (r1 + 1 < m) A[r1 ^ (sa | 4)] = (T)(n1 - a1);
+    if (r0 + 1 < m) {
+      A[r0 ^ sa] = (T)d0;
+      vmn = min(vmn, d0);
+      vmx = max(vmx, d0);
+    }
+    if (r1 + 1 < m) {
+      A[r1 ^ (sa | 4)] = (T)d1;
+      vmn = min(vmn, d1);
+      vmx = max(vmx, d1);
+    }
   }
   __syncwarp();
 
   uint32_t ob_counts, ob_vals;
-  if (!write_array<uint16_t, N>(C, m, out + cur, limit - cur, use_bp, ob_counts)) return false;
-  cur += (ob_counts + 3u) & ~3u;
-  if (!write_array<T, N>(A, m - 1, out + cur, limit - cur, use_bp, ob_vals)) return false;
-  cur += (ob_vals + 3u) & ~3u;
+  if (use_bp) {
+    cmn = __reduce_min_sync(kFull, cmn);
+    cmx = __reduce_max_sync(kFull, cmx);
+    vmn = __reduce_min_sync(kFull, vmn);
+    vmx = __reduce_max_sync(kFull, vmx);
+    if (m == 1) vmn = vmx = 0; // empty delta array: frame 0, width 0
+    // padding up to the next multiple of 32 packs as zero
+    {
+      const int rc = (m & ~31) + lane;
+      if (rc >= m && (m & 31)) C[Swz<uint16_t>::p(rc)] = (uint16_t)cmn;
+      const int nv = m - 1;
+      const int rv = (nv & ~31) + lane;
+      if (rv >= nv && (nv & 31)) A[Swz<T>::p(rv)] = (T)vmn;
+    }
+    __syncwarp();
+    if (!write_packed_known<uint16_t>(C, m, cmn, cmx, out + cur, limit - cur, ob_counts)) return false;
+    cur += (ob_counts + 3u) & ~3u;
+    if (!write_packed_known<T>(A, m - 1, vmn, vmx, out + cur, limit - cur, ob_vals)) return false;
+    cur += (ob_vals + 3u) & ~3u;
+  } else {
+    if (!write_array<uint16_t, N>(C, m, out + cur, limit - cur, false, ob_counts)) return false;
+    cur += (ob_counts + 3u) & ~3u;
+    if (!write_array<T, N>(A, m - 1, out + cur, limit - cur, false, ob_vals)) return false;
+    cur += (ob_vals + 3u) & ~3u;
+  }
   if (lane == 0) {
     uint32_t* mw = reinterpret_cast<uint32_t*>(out + chunk_start);
     mw[0] = (uint32_t)(cur - chunk_start);
@@ -837,7 +915,7 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, B200_CASC_COMP_MINB)
 compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
                 size_t batch, int type_id, int R, int D, int bp)
 {
