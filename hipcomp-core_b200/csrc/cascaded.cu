@@ -938,6 +938,88 @@ struct DecompSmem {
   static constexpr int BYTES = kChunkBytes + 2 * (N * 2); // values, run counts/starts, run-index marks
 };
 
+// Fused fast path of the decoder for num_RLEs = 1, num_deltas = 1, bit-packed, 4-byte elements, when the
+// chunk expands to exactly one full 4096-byte chunk and the destination is 16-byte aligned.
+// out[i] = seed + sum of the deltas of all runs that start at or before i, so instead of decoding the run
+// values, marking run starts and gathering, the deltas are scattered (added) onto the run start positions of
+// a zeroed shared-memory array and ONE prefix sum over the 1024 positions - held as 8 coalesced 16-byte
+// vectors per lane - produces the output, which goes to global memory straight from registers.
+// Empty runs add onto the next run's start, which is what skipping them means.
+// Returns false when a precondition does not hold: nothing was written and the generic path decides.
+template <typename T>
+__device__ bool decompress_chunk_r1d1(const uint8_t* cptr, uint32_t cb, const uint8_t* vptr, uint32_t vb, T seed,
+                                      T* gout, T* O)
+{
+  static_assert(sizeof(T) == 4, "fast path is for 4-byte elements");
+  constexpr uint32_t N = kChunkBytes / 4;
+  const int lane = lane_id();
+  if (cb < 8 || vb < 8) return false;
+  const uint32_t* cw = reinterpret_cast<const uint32_t*>(cptr);
+  const uint32_t* vw = reinterpret_cast<const uint32_t*>(vptr);
+  const uint32_t cfr = __ldg(cw), cmeta = __ldg(cw + 1), vfr = __ldg(vw), vmeta = __ldg(vw + 1);
+  const uint32_t cbw = cmeta >> 16, nc = cmeta & 0xffffu, vbw = vmeta >> 16, nv = vmeta & 0xffffu;
+  if (nc > N || cbw > 16 || nv + 1 > N || vbw > 32 || nc < nv + 1) return false;
+  const int cwords = (int)((nc * cbw + 31u) >> 5), vwords = (int)((nv * vbw + 31u) >> 5);
+  if (8u + 4u * (uint32_t)cwords > ((cb + 3u) & ~3u) || 8u + 4u * (uint32_t)vwords > ((vb + 3u) & ~3u)) return false;
+  const int m = (int)nv + 1;
+
+  uint4* O4 = reinterpret_cast<uint4*>(O);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) O4[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+  __syncwarp();
+
+  uint32_t carry = 0;
+  for (int t = 0; t * 32 < m; ++t) {
+    const int r = 32 * t + lane;
+    uint32_t len = 0;
+    T d = 0;
+    if (r < m) {
+      len = (uint32_t)(uint16_t)((cbw ? get_bits32(cw + 2, cwords, (uint32_t)r * cbw, cbw) : 0u) + cfr);
+      d = r == 0 ? seed : (T)((vbw ? get_bits32(vw + 2, vwords, (uint32_t)(r - 1) * vbw, vbw) : 0u) + vfr);
+    }
+    uint32_t total;
+    const uint32_t start = carry + warp_excl_sum<uint32_t>(len, total);
+    carry += total;
+    if (carry > N) return false;
+    if (r < m && start < N) atomicAdd(reinterpret_cast<uint32_t*>(O) + start, (uint32_t)d);
+  }
+  if (carry != N) return false;
+  __syncwarp();
+
+  uint4 q[8];
+  uint32_t s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    q[k] = O4[lane + 32 * k];
+    q[k].y += q[k].x;
+    q[k].z += q[k].y;
+    q[k].w += q[k].z;
+    s[k] = q[k].w;
+  }
+#pragma unroll
+  for (int dd = 1; dd < 32; dd <<= 1) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t o = __shfl_up_sync(kFull, s[k], dd);
+      if (lane >= dd) s[k] += o;
+    }
+  }
+  uint32_t tile_base = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t tot = __shfl_sync(kFull, s[k], 31);
+    const uint32_t ex = s[k] - q[k].w + tile_base;
+    q[k].x += ex;
+    q[k].y += ex;
+    q[k].z += ex;
+    q[k].w += ex;
+    tile_base += tot;
+    st_stream16(reinterpret_cast<uint4*>(gout) + lane + 32 * k, q[k]);
+  }
+  __syncwarp();
+  return true;
+}
+
 // One warp decompresses one partition.  (reference cascaded_decompression_fcn :1106-1435)
 template <typename T>
 __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* out, size_t out_cap,
@@ -999,6 +1081,20 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
       const size_t final_pos = arrays + off[R];
       if (final_pos + ((final_bytes + 3u) & ~3u) > end) { ok = false; break; }
       int n;
+      if constexpr (sizeof(T) == 4) {
+        if (R == 1 && D == 1 && bp != 0 && n_total - done >= (size_t)N &&
+            (reinterpret_cast<uintptr_t>(out + done) & 15) == 0) {
+          const uint32_t cb = __ldg(mw + 1);
+          if (arrays + ((cb + 3u) & ~3u) <= end &&
+              decompress_chunk_r1d1<T>(comp + arrays, cb, comp + final_pos, final_bytes,
+                                       *reinterpret_cast<const T*>(comp + chunk + delta_off), out + done, A)) {
+            done += (size_t)N;
+            if (chunk_bytes < (uint32_t)msize) { ok = false; break; }
+            chunk = (chunk + (chunk_bytes & ~3u) + W - 1) / W * W;
+            continue;
+          }
+        }
+      }
       if (!read_array<T, N>(comp + final_pos, final_bytes, bp != 0, A, n)) { ok = false; break; }
       __syncwarp();
       bool wrote_global = false;
