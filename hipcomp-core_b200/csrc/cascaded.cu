@@ -947,26 +947,46 @@ struct DecompSmem {
 // Empty runs add onto the next run's start, which is what skipping them means.
 // Returns false when a precondition does not hold: nothing was written and the generic path decides.
 template <typename T>
-__device__ bool decompress_chunk_r1d1(const uint8_t* cptr, uint32_t cb, const uint8_t* vptr, uint32_t vb, T seed,
-                                      T* gout, T* O)
+__device__ bool decompress_chunk_r1d1(const uint8_t* chunk_ptr, uint32_t avail_words, T* gout, T* O, uint32_t* S,
+                                      uint32_t& chunk_bytes)
 {
   static_assert(sizeof(T) == 4, "fast path is for 4-byte elements");
   constexpr uint32_t N = kChunkBytes / 4;
+  constexpr uint32_t kStageWords = 1024; // the C + I regions of the warp's shared memory
   const int lane = lane_id();
-  if (cb < 8 || vb < 8) return false;
-  const uint32_t* cw = reinterpret_cast<const uint32_t*>(cptr);
-  const uint32_t* vw = reinterpret_cast<const uint32_t*>(vptr);
-  const uint32_t cfr = __ldg(cw), cmeta = __ldg(cw + 1), vfr = __ldg(vw), vmeta = __ldg(vw + 1);
+  // stage the compressed chunk in shared memory: one round of independent coalesced loads covers the
+  // first KiB (a C3 chunk is ~500 bytes); the unpack loops below then never wait on global memory
+  const uint32_t* gw = reinterpret_cast<const uint32_t*>(chunk_ptr);
+  const uint32_t first = avail_words < 256u ? avail_words : 256u;
+  uint32_t w[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) w[k] = (uint32_t)(lane + 32 * k) < first ? __ldg(gw + lane + 32 * k) : 0u;
+  __syncwarp(); // earlier readers of S are done
+#pragma unroll
+  for (int k = 0; k < 8; ++k) S[lane + 32 * k] = w[k];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) reinterpret_cast<uint4*>(O)[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+  __syncwarp();
+  chunk_bytes = S[0];
+  const uint32_t cb = S[1], vb = S[2];
+  const T seed = (T)S[3];
+  const uint32_t cpad = (cb + 3u) & ~3u, vpad = (vb + 3u) & ~3u;
+  if (cb < 8 || vb < 8 || cb > 4096 || vb > 4096) return false;
+  const uint32_t need = (16u + cpad + vpad) >> 2; // words of metadata + both arrays
+  if (need > avail_words || need + 1 > kStageWords) return false; // + 1: the unpack may touch one word more
+  if (need > 256u) {
+    for (uint32_t i = 256u + (uint32_t)lane; i < need; i += 32) S[i] = __ldg(gw + i);
+    __syncwarp();
+  }
+  const uint32_t* cw = S + 4;
+  const uint32_t* vw = S + 4 + (cpad >> 2);
+  const uint32_t cfr = cw[0], cmeta = cw[1], vfr = vw[0], vmeta = vw[1];
   const uint32_t cbw = cmeta >> 16, nc = cmeta & 0xffffu, vbw = vmeta >> 16, nv = vmeta & 0xffffu;
   if (nc > N || cbw > 16 || nv + 1 > N || vbw > 32 || nc < nv + 1) return false;
-  const int cwords = (int)((nc * cbw + 31u) >> 5), vwords = (int)((nv * vbw + 31u) >> 5);
-  if (8u + 4u * (uint32_t)cwords > ((cb + 3u) & ~3u) || 8u + 4u * (uint32_t)vwords > ((vb + 3u) & ~3u)) return false;
+  const uint32_t cwords = (nc * cbw + 31u) >> 5, vwords = (nv * vbw + 31u) >> 5;
+  if (8u + 4u * cwords > cpad || 8u + 4u * vwords > vpad) return false;
   const int m = (int)nv + 1;
-
-  uint4* O4 = reinterpret_cast<uint4*>(O);
-#pragma unroll
-  for (int k = 0; k < 8; ++k) O4[lane + 32 * k] = make_uint4(0, 0, 0, 0);
-  __syncwarp();
+  const uint32_t cmask = cbw >= 32 ? ~0u : (1u << cbw) - 1u, vmask = vbw >= 32 ? ~0u : (1u << vbw) - 1u;
 
   uint32_t carry = 0;
   for (int t = 0; t * 32 < m; ++t) {
@@ -974,18 +994,23 @@ __device__ bool decompress_chunk_r1d1(const uint8_t* cptr, uint32_t cb, const ui
     uint32_t len = 0;
     T d = 0;
     if (r < m) {
-      len = (uint32_t)(uint16_t)((cbw ? get_bits32(cw + 2, cwords, (uint32_t)r * cbw, cbw) : 0u) + cfr);
-      d = r == 0 ? seed : (T)((vbw ? get_bits32(vw + 2, vwords, (uint32_t)(r - 1) * vbw, vbw) : 0u) + vfr);
+      // a value that straddles two words has its second word inside the array; otherwise the extra word
+      // read is masked off (it is still inside S)
+      const uint32_t cp = (uint32_t)r * cbw, vp = (uint32_t)(r > 0 ? r - 1 : 0) * vbw;
+      const uint32_t cv = __funnelshift_r(cw[2 + (cp >> 5)], cw[3 + (cp >> 5)], cp & 31) & cmask;
+      const uint32_t vv = __funnelshift_r(vw[2 + (vp >> 5)], vw[3 + (vp >> 5)], vp & 31) & vmask;
+      len = (uint32_t)(uint16_t)(cv + cfr);
+      d = r == 0 ? seed : (T)(vv + vfr);
     }
     uint32_t total;
     const uint32_t start = carry + warp_excl_sum<uint32_t>(len, total);
     carry += total;
-    if (carry > N) return false;
     if (r < m && start < N) atomicAdd(reinterpret_cast<uint32_t*>(O) + start, (uint32_t)d);
   }
   if (carry != N) return false;
   __syncwarp();
 
+  const uint4* O4 = reinterpret_cast<const uint4*>(O);
   uint4 q[8];
   uint32_t s[8];
 #pragma unroll
@@ -1065,6 +1090,19 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
     size_t chunk = 8;
     while (chunk < end) {
       if (chunk + msize > end) { ok = false; break; }
+      if constexpr (sizeof(T) == 4) {
+        if (R == 1 && D == 1 && bp != 0 && n_total - done >= (size_t)N &&
+            (reinterpret_cast<uintptr_t>(out + done) & 15) == 0) {
+          uint32_t cbytes;
+          if (decompress_chunk_r1d1<T>(comp + chunk, (uint32_t)((end - chunk) >> 2), out + done, A,
+                                       reinterpret_cast<uint32_t*>(C), cbytes)) {
+            done += (size_t)N;
+            if (cbytes < (uint32_t)msize) { ok = false; break; }
+            chunk = (chunk + (cbytes & ~3u) + W - 1) / W * W;
+            continue;
+          }
+        }
+      }
       const uint32_t* mw = reinterpret_cast<const uint32_t*>(comp + chunk);
       const uint32_t chunk_bytes = __ldg(mw);
       uint32_t off[9];
@@ -1081,20 +1119,6 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
       const size_t final_pos = arrays + off[R];
       if (final_pos + ((final_bytes + 3u) & ~3u) > end) { ok = false; break; }
       int n;
-      if constexpr (sizeof(T) == 4) {
-        if (R == 1 && D == 1 && bp != 0 && n_total - done >= (size_t)N &&
-            (reinterpret_cast<uintptr_t>(out + done) & 15) == 0) {
-          const uint32_t cb = __ldg(mw + 1);
-          if (arrays + ((cb + 3u) & ~3u) <= end &&
-              decompress_chunk_r1d1<T>(comp + arrays, cb, comp + final_pos, final_bytes,
-                                       *reinterpret_cast<const T*>(comp + chunk + delta_off), out + done, A)) {
-            done += (size_t)N;
-            if (chunk_bytes < (uint32_t)msize) { ok = false; break; }
-            chunk = (chunk + (chunk_bytes & ~3u) + W - 1) / W * W;
-            continue;
-          }
-        }
-      }
       if (!read_array<T, N>(comp + final_pos, final_bytes, bp != 0, A, n)) { ok = false; break; }
       __syncwarp();
       bool wrote_global = false;
