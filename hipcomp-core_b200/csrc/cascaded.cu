@@ -305,8 +305,20 @@ __device__ __forceinline__ bool write_packed_known(const E* arr, int n, int32_t 
 #pragma unroll
     for (int j = 0; j < 32 / VE; ++j) {
       const Vec<E> v = ld_vec<E>(arr, (g << 5) + j * VE);
+      if (sizeof(E) == 2) {
+        // two 16-bit lanes per SIMD subtract
+        const uint32_t fr2 = (uint32_t)fr * 0x10001u;
+        const uint32_t w4[4] = {v.q.x, v.q.y, v.q.z, v.q.w};
 #pragma unroll
-      for (int c = 0; c < VE; ++c) d[j * VE + c] = (uint32_t)(E)(v.e[c] - fr);
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t x = __vsub2(w4[c], fr2);
+          d[j * 8 + 2 * c] = x & 0xffffu;
+          d[j * 8 + 2 * c + 1] = x >> 16;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < VE; ++c) d[j * VE + c] = (uint32_t)(E)(v.e[c] - fr);
+      }
     }
     pack32_dispatch<sizeof(E) == 2 ? 16 : 32>(bw, d, outw + 2, g * (int)bw, words);
   }
@@ -988,24 +1000,43 @@ __device__ bool decompress_chunk_r1d1(const uint8_t* chunk_ptr, uint32_t avail_w
   const int m = (int)nv + 1;
   const uint32_t cmask = cbw >= 32 ? ~0u : (1u << cbw) - 1u, vmask = vbw >= 32 ? ~0u : (1u << vbw) - 1u;
 
+  // 64 runs per step (two per lane): the two length scans travel as one word of two 16-bit sums
   uint32_t carry = 0;
-  for (int t = 0; t * 32 < m; ++t) {
-    const int r = 32 * t + lane;
-    uint32_t len = 0;
-    T d = 0;
-    if (r < m) {
-      // a value that straddles two words has its second word inside the array; otherwise the extra word
-      // read is masked off (it is still inside S)
-      const uint32_t cp = (uint32_t)r * cbw, vp = (uint32_t)(r > 0 ? r - 1 : 0) * vbw;
+  for (int u = 0; u * 64 < m; ++u) {
+    const int r0 = 64 * u + lane, r1 = r0 + 32;
+    uint32_t len0 = 0, len1 = 0;
+    T d0 = 0, d1 = 0;
+    // a value that straddles two words has its second word inside the array; otherwise the extra word
+    // read is masked off (it is still inside S)
+    if (r0 < m) {
+      const uint32_t cp = (uint32_t)r0 * cbw, vp = (uint32_t)(r0 > 0 ? r0 - 1 : 0) * vbw;
       const uint32_t cv = __funnelshift_r(cw[2 + (cp >> 5)], cw[3 + (cp >> 5)], cp & 31) & cmask;
       const uint32_t vv = __funnelshift_r(vw[2 + (vp >> 5)], vw[3 + (vp >> 5)], vp & 31) & vmask;
-      len = (uint32_t)(uint16_t)(cv + cfr);
-      d = r == 0 ? seed : (T)(vv + vfr);
+      len0 = (uint32_t)(uint16_t)(cv + cfr);
+      d0 = r0 == 0 ? seed : (T)(vv + vfr);
     }
-    uint32_t total;
-    const uint32_t start = carry + warp_excl_sum<uint32_t>(len, total);
-    carry += total;
-    if (r < m && start < N) atomicAdd(reinterpret_cast<uint32_t*>(O) + start, (uint32_t)d);
+    if (r1 < m) {
+      const uint32_t cp = (uint32_t)r1 * cbw, vp = (uint32_t)(r1 - 1) * vbw;
+      const uint32_t cv = __funnelshift_r(cw[2 + (cp >> 5)], cw[3 + (cp >> 5)], cp & 31) & cmask;
+      const uint32_t vv = __funnelshift_r(vw[2 + (vp >> 5)], vw[3 + (vp >> 5)], vp & 31) & vmask;
+      len1 = (uint32_t)(uint16_t)(cv + cfr);
+      d1 = (T)(vv + vfr);
+    }
+    if (__any_sync(kFull, len0 > N || len1 > N)) return false; // keeps each 16-bit sum below 2^16
+    const uint32_t packed = len0 | (len1 << 16);
+    uint32_t incl = packed;
+#pragma unroll
+    for (int dd = 1; dd < 32; dd <<= 1) {
+      const uint32_t o = __shfl_up_sync(kFull, incl, dd);
+      if (lane >= dd) incl += o;
+    }
+    const uint32_t tot = __shfl_sync(kFull, incl, 31);
+    const uint32_t ex = incl - packed;
+    const uint32_t start0 = carry + (ex & 0xffffu);
+    const uint32_t start1 = carry + (tot & 0xffffu) + (ex >> 16);
+    carry += (tot & 0xffffu) + (tot >> 16);
+    if (r0 < m && start0 < N) atomicAdd(reinterpret_cast<uint32_t*>(O) + start0, (uint32_t)d0);
+    if (r1 < m && start1 < N) atomicAdd(reinterpret_cast<uint32_t*>(O) + start1, (uint32_t)d1);
   }
   if (carry != N) return false;
   __syncwarp();
