@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--cpu-sample-mib", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--data", default="default", choices=["default", "zeros", "random", "text", "logs", "ints"],
+                    help="input class (C5 sweep); default = the codec's BASELINE config generator")
+    ap.add_argument("--casc-opts", default="1,1,1", help="cascaded num_RLEs,num_deltas,use_bp (C3 = 1,1,1; library default 2,1,1)")
     ap.add_argument("--e2e-slices", type=int, default=4, help="slices the e2e path pipelines over its streams")
     return ap.parse_args()
 
@@ -213,6 +216,18 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- GPU arm
+def load_traffic(codec, direction, nbytes):
+    """DRAM bytes per launch of the dominant kernel, from the committed `ncu --set full` capture
+    (profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one launch and the uncompressed
+    bytes that launch processed), scaled to this run's bytes per launch.  None when no capture is recorded."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[codec][direction]
+        return {"traffic": t["dram_bytes"] / t["uncompressed_bytes"] * nbytes / GB, "traffic_unit": "GB per launch",
+                "traffic_source": t["source"]}
+    except Exception:
+        return {"traffic": None}
+
+
 def load_peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
@@ -264,6 +279,15 @@ def make_data(args, wl, rank, device):
     S = importlib.import_module("hipcomp-core_b200.synth")
     nbytes = wl["size_mib"] << 20
     seed = wl["seed"] + 1000 * rank
+    data = getattr(args, "data", "default")
+    if data == "zeros":
+        return torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    if data == "random":
+        g = torch.Generator(device=device)
+        g.manual_seed(seed)
+        return torch.randint(0, 256, (nbytes,), dtype=torch.uint8, device=device, generator=g)
+    gen = {"text": "zipf_text", "logs": "log_lines", "ints": "sorted_ints"}.get(data, wl["gen"])
+    wl = dict(wl, gen=gen)
     if wl["gen"] == "log_lines":
         return S.log_lines(nbytes, seed, device)
     if wl["gen"] == "zipf_text":
@@ -274,14 +298,14 @@ def make_data(args, wl, rank, device):
 class Plan:
     """Pre-allocated buffers + argument lists so the timed loop is just the two C-ABI calls."""
 
-    def __init__(self, codec, raw, chunk):
+    def __init__(self, codec, raw, chunk, casc_opts=(1, 1, 1)):
         B = importlib.import_module("hipcomp-core_b200.batched")
         L = importlib.import_module("hipcomp-core_b200._lib")
         self.B, self.L, self.codec, self.chunk = B, L, codec, chunk
         dev = raw.device
         self.n = raw.numel() // chunk
         self.raw = raw
-        self.opts = L.CascadedOpts(4096, L.TYPE_INT, 1, 1, 1) if codec == "cascaded" else B.default_opts(codec)
+        self.opts = L.CascadedOpts(4096, L.TYPE_INT, *casc_opts) if codec == "cascaded" else B.default_opts(codec)
         off = np.arange(self.n, dtype=np.int64) * chunk
         self.src = B.DeviceBatch(raw, off, np.full(self.n, chunk, np.int64))
         self.stride = (B.max_compressed_chunk_bytes(codec, chunk, self.opts) + 15) // 16 * 16
@@ -344,7 +368,8 @@ def run_b200(args):
     device = torch.device("cuda", local)
     raw = make_data(args, wl, rank, device)
     nbytes = raw.numel()
-    plan = Plan(args.codec, raw, wl["chunk"])
+    casc_opts = tuple(int(x) for x in args.casc_opts.split(","))
+    plan = Plan(args.codec, raw, wl["chunk"], casc_opts)
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     for _ in range(max(args.warmup, 3)):
@@ -409,7 +434,9 @@ def run_b200(args):
         "vs_baseline": None,
         "dtype": "u8" if args.codec != "cascaded" else "int32",
         "data": "synthetic",
-        "config": {"workload": wl["name"], "bytes_per_gpu": nbytes, "chunk_bytes": wl["chunk"],
+        "config": {"workload": wl["name"] + ("" if args.data == "default" else f" [input class: {args.data}]")
+                   + ("" if args.codec != "cascaded" or casc_opts == (1, 1, 1) else f" [opts {args.casc_opts}]"),
+                   "bytes_per_gpu": nbytes, "chunk_bytes": wl["chunk"],
                    "chunks_per_gpu": plan.n, "sharding": f"{world} rank(s), independent chunk ranges, no collective",
                    "l2": "inputs (>= 1 GiB per step) larger than the 126 MB L2; no explicit flush",
                    "seed": wl["seed"]},
@@ -417,7 +444,7 @@ def run_b200(args):
         "decompress_GBps": total_bytes * K / t_dec_max / GB,
         "compression_ratio": total_bytes / total_comp,
         "roofline": {"bound": "hbm", "kernel": f"{args.codec}::{dominant}_kernel", "achieved": ach, "peak": peak,
-                     "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": ach / peak, **load_traffic(args.codec, dominant, nbytes), "peak_source": peak_src,
                      "ms_per_launch": comp_ms if dominant == "compress" else dec_ms},
         "roofline_decompress": {"bound": "hbm", "achieved": alg_dec / (t_dec / K) / GB, "peak": peak, "unit": "GB/s",
                                 "frac": alg_dec / (t_dec / K) / GB / peak, "ms_per_launch": dec_ms},

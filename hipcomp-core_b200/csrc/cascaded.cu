@@ -662,11 +662,7 @@ __device__ void raw_copy(const T* in, size_t n, uint8_t* out)
   const size_t bytes = n * sizeof(T);
   const uint8_t* src = reinterpret_cast<const uint8_t*>(in);
   uint8_t* dst = out + 8;
-  if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
-    const size_t v = bytes / 16;
-    for (size_t i = lane; i < v; i += 32) st_stream16(dst + 16 * i, ld_stream16(src + 16 * i));
-    for (size_t i = v * 16 + lane; i < bytes; i += 32) dst[i] = src[i];
-  } else {
+  if (!warp_copy_stream(dst, src, bytes)) {
     T* d = reinterpret_cast<T*>(dst);
     for (size_t i = lane; i < n; i += 32) d[i] = in[i];
   }
@@ -1103,11 +1099,7 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
       const uint8_t* src = comp + 8;
       uint8_t* dst = reinterpret_cast<uint8_t*>(out);
       const size_t bytes = n_total * W;
-      if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
-        const size_t v = bytes / 16;
-        for (size_t i = lane; i < v; i += 32) st_stream16(dst + 16 * i, ld_stream16(src + 16 * i));
-        for (size_t i = v * 16 + lane; i < bytes; i += 32) dst[i] = src[i];
-      } else {
+      if (!warp_copy_stream(dst, src, bytes)) {
         const T* s = reinterpret_cast<const T*>(src);
         for (size_t i = lane; i < n_total; i += 32) out[i] = s[i];
       }

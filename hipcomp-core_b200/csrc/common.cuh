@@ -133,4 +133,60 @@ __device__ __forceinline__ void st_stream16(void* p, uint4 v)
                : "memory");
 }
 
+// 16 source bytes at a 16-, 8- or 4-byte aligned address (A = guaranteed alignment), streamed past L1
+template <int A>
+__device__ __forceinline__ uint4 ld_stream16_a(const uint8_t* p)
+{
+  uint4 r;
+  if (A >= 16) {
+    r = ld_stream16(p);
+  } else if (A == 8) {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.z), "=r"(r.w) : "l"(p + 8));
+  } else {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(p);
+    r.x = __ldg(w); r.y = __ldg(w + 1); r.z = __ldg(w + 2); r.w = __ldg(w + 3);
+  }
+  return r;
+}
+
+template <int A>
+__device__ __forceinline__ void warp_copy_vecs(uint8_t* dst, const uint8_t* src, size_t vecs)
+{
+  size_t v = (size_t)lane_id();
+  // four independent 16-byte loads in flight per lane
+  for (; v + 96 < vecs; v += 128) {
+    const uint4 a = ld_stream16_a<A>(src + 16 * v), b = ld_stream16_a<A>(src + 16 * (v + 32)),
+                c = ld_stream16_a<A>(src + 16 * (v + 64)), d = ld_stream16_a<A>(src + 16 * (v + 96));
+    st_stream16(dst + 16 * v, a);
+    st_stream16(dst + 16 * (v + 32), b);
+    st_stream16(dst + 16 * (v + 64), c);
+    st_stream16(dst + 16 * (v + 96), d);
+  }
+  for (; v < vecs; v += 32) st_stream16(dst + 16 * v, ld_stream16_a<A>(src + 16 * v));
+}
+
+// Warp-cooperative bulk copy of read-only global memory (raw / fallback partitions).  Requires src and
+// dst to be congruent modulo 4; returns false (nothing copied) otherwise.  Stores are 16 bytes wide,
+// loads as wide as the source alignment allows.
+__device__ __forceinline__ bool warp_copy_stream(uint8_t* dst, const uint8_t* src, size_t n)
+{
+  if ((reinterpret_cast<uintptr_t>(dst) ^ reinterpret_cast<uintptr_t>(src)) & 3) return false;
+  const size_t lane = (size_t)lane_id();
+  size_t head = (size_t)((16 - (reinterpret_cast<uintptr_t>(dst) & 15)) & 15);
+  if (head > n) head = n;
+  if (lane < head) dst[lane] = __ldg(src + lane);
+  dst += head;
+  src += head;
+  n -= head;
+  const size_t vecs = n >> 4;
+  const unsigned sa = (unsigned)(reinterpret_cast<uintptr_t>(src) & 15);
+  if (sa == 0) warp_copy_vecs<16>(dst, src, vecs);
+  else if (sa == 8) warp_copy_vecs<8>(dst, src, vecs);
+  else warp_copy_vecs<4>(dst, src, vecs);
+  const size_t i = (vecs << 4) + lane;
+  if (i < n) dst[i] = __ldg(src + i);
+  return true;
+}
+
 } // namespace b200comp
