@@ -680,13 +680,13 @@ __device__ void raw_copy(const T* in, size_t n, uint8_t* out)
 // Returns false when the chunk does not fit (caller falls back to the raw partition).
 template <typename T>
 __device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, size_t limit, bool use_bp, T* A,
-                                    uint16_t* C)
+                                    uint16_t* C, int R)
 {
   static_assert(sizeof(T) == 4, "fast path is for 4-byte elements");
   constexpr int N = kChunkBytes / 4;
   const int lane = lane_id();
   const size_t chunk_start = cur;
-  cur += 16; // meta_size(4, 1, 1)
+  cur += 12 + 4 * R; // meta_size(4, R, 1)
   if (cur > limit) return false;
 
   uint4 v[8];
@@ -791,6 +791,39 @@ __device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, siz
   __syncwarp();
 
   uint32_t ob_counts, ob_vals;
+  if (R == 2) {
+    // num_RLEs = 2 (the library's default option set): the first RLE + delta above are shared; the
+    // deltas then take the generic second run-length layer.  Same calls, same order, same bytes as the
+    // layer loop of compress_partition.
+    if (use_bp) {
+      cmn = __reduce_min_sync(kFull, cmn);
+      cmx = __reduce_max_sync(kFull, cmx);
+      const int rc = (m & ~31) + lane;
+      if (rc >= m && (m & 31)) C[Swz<uint16_t>::p(rc)] = (uint16_t)cmn;
+      __syncwarp();
+      if (!write_packed_known<uint16_t>(C, m, cmn, cmx, out + cur, limit - cur, ob_counts)) return false;
+    } else {
+      if (!write_array<uint16_t, N>(C, m, out + cur, limit - cur, false, ob_counts)) return false;
+    }
+    cur += (ob_counts + 3u) & ~3u;
+    __syncwarp();
+    const int n2 = rle_encode<T, N>(A, m - 1, C);
+    uint32_t ob_counts2;
+    if (!write_array<uint16_t, N>(C, n2, out + cur, limit - cur, use_bp, ob_counts2)) return false;
+    cur += (ob_counts2 + 3u) & ~3u;
+    if (!write_array<T, N>(A, n2, out + cur, limit - cur, use_bp, ob_vals)) return false;
+    cur += (ob_vals + 3u) & ~3u;
+    if (lane == 0) {
+      uint32_t* mw = reinterpret_cast<uint32_t*>(out + chunk_start);
+      mw[0] = (uint32_t)(cur - chunk_start);
+      mw[1] = ob_counts;
+      mw[2] = ob_counts2;
+      mw[3] = ob_vals;
+      mw[4] = (uint32_t)seed;
+    }
+    __syncwarp();
+    return true;
+  }
   if (use_bp) {
     cmn = __reduce_min_sync(kFull, cmn);
     cmx = __reduce_max_sync(kFull, cmx);
@@ -852,12 +885,12 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
   size_t cur = 8;
   const int layers = R > D ? R : D;
 
-  const bool fast_r1d1 = W == 4 && R == 1 && D == 1 && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
+  const bool fast_r1d1 = W == 4 && (R == 1 || R == 2) && D == 1 && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
 
   for (size_t c = 0; c < n_chunks && use_compression; ++c) {
     if constexpr (sizeof(T) == 4) {
       if (fast_r1d1 && n_total - c * N >= (size_t)N) {
-        if (!compress_chunk_r1d1<T>(in + c * N, out, cur, limit, bp != 0, A, C)) use_compression = false;
+        if (!compress_chunk_r1d1<T>(in + c * N, out, cur, limit, bp != 0, A, C, R)) use_compression = false;
         continue;
       }
     }
