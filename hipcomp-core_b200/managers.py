@@ -7,6 +7,7 @@ configure_decompression -> decompress, with a status word per config.  Buffers a
 CUDA tensors; nothing here computes — every call lands in libhipcomp.so.
 """
 import ctypes as C
+import weakref
 
 import torch
 
@@ -38,10 +39,12 @@ class CompressionConfig:
     def get_status(self):
         return L.lib().b200compCompConfigStatus(self._h)
 
-    def __del__(self):
+    def _destroy(self):
         if getattr(self, "_h", None):
             L.lib().b200compCompConfigDestroy(self._h)
             self._h = None
+
+    __del__ = _destroy
 
 
 class DecompressionConfig:
@@ -53,10 +56,12 @@ class DecompressionConfig:
     def get_status(self):
         return L.lib().b200compDecompConfigStatus(self._h)
 
-    def __del__(self):
+    def _destroy(self):
         if getattr(self, "_h", None):
             L.lib().b200compDecompConfigDestroy(self._h)
             self._h = None
+
+    __del__ = _destroy
 
 
 class Manager:
@@ -65,12 +70,19 @@ class Manager:
     def __init__(self, handle, stream=None):
         self._h = handle
         self._stream = stream
+        # a config hands its pinned status word back to the manager's pool when it dies (as in the reference,
+        # PinnedPtrs.hpp:70-211), so the manager must outlive its configs: close() retires them first
+        self._configs = weakref.WeakSet()
+
+    def _track(self, cfg):
+        self._configs.add(cfg)
+        return cfg
 
     def configure_compression(self, decomp_buffer_size):
         h, mx, n = C.c_void_p(), C.c_size_t(), C.c_size_t()
         _ck(L.lib().b200compManagerConfigureCompression(self._h, decomp_buffer_size, C.byref(h), C.byref(mx), C.byref(n)),
             "configure_compression")
-        return CompressionConfig(h, decomp_buffer_size, mx.value, n.value)
+        return self._track(CompressionConfig(h, decomp_buffer_size, mx.value, n.value))
 
     def compress(self, decomp_buffer, comp_buffer, comp_config):
         _ck(L.lib().b200compManagerCompress(self._h, decomp_buffer.data_ptr(), comp_buffer.data_ptr(), comp_config._h), "compress")
@@ -83,7 +95,7 @@ class Manager:
         else:
             _ck(L.lib().b200compManagerConfigureDecompression(self._h, arg.data_ptr(), C.byref(h), C.byref(sz), C.byref(n)),
                 "configure_decompression")
-        return DecompressionConfig(h, sz.value, n.value)
+        return self._track(DecompressionConfig(h, sz.value, n.value))
 
     def decompress(self, decomp_buffer, comp_buffer, decomp_config):
         _ck(L.lib().b200compManagerDecompress(self._h, decomp_buffer.data_ptr(), comp_buffer.data_ptr(), decomp_config._h),
@@ -106,6 +118,8 @@ class Manager:
 
     def close(self):
         if getattr(self, "_h", None):
+            for cfg in list(getattr(self, "_configs", ())):
+                cfg._destroy()
             L.lib().b200compManagerDestroy(self._h)
             self._h = None
 
