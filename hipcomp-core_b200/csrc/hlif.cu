@@ -226,6 +226,9 @@ struct HeaderFill {
 
 // offsets[i] = cursor + exclusive sum of the (padded) sizes of the wave; cursor += total.
 // One CTA: the scan is a few microseconds next to the encode of the same wave.
+constexpr int kPlaceItems = 8;                                  // chunks per lane per round
+constexpr int kPlaceStage = 32 * kPlaceItems + 32;              // stage elements per warp (one pad per 8)
+constexpr size_t kPlaceSmem = (size_t)32 * kPlaceStage * sizeof(unsigned long long);
 __global__ void __launch_bounds__(1024)
 place_kernel(const size_t* sizes, size_t* offsets, size_t n, unsigned long long* cursor, size_t align, HeaderFill hf)
 {
@@ -253,11 +256,33 @@ place_kernel(const size_t* sizes, size_t* offsets, size_t n, unsigned long long*
   }
   __syncthreads();
   unsigned long long base = base_s;
-  for (size_t tile = 0; tile < n; tile += 1024) {
-    const size_t i = tile + threadIdx.x;
-    unsigned long long v = 0;
-    if (i < n) v = (sizes[i] + align - 1) / align * align;
-    unsigned long long incl = v;
+  // Each warp owns 256 consecutive chunks per round.  Sizes are loaded coalesced, transposed through a padded
+  // shared-memory stage so that every lane sums 8 consecutive chunks in registers, scanned once per round
+  // (warp shuffle + 32 warp totals), and the offsets go back through the same stage to coalesced stores.
+  // A 256 Ki-chunk wave (1 GiB of 4 KiB cascaded chunks) is 32 rounds.
+  constexpr int kItems = kPlaceItems;
+  const bool pow2 = (align & (align - 1)) == 0; // 1, 4 or 8 in practice: no 64-bit division per chunk
+  extern __shared__ unsigned long long place_stage[];
+  unsigned long long* stage = place_stage + (size_t)warp * kPlaceStage;
+  for (size_t tile = 0; tile < n; tile += 1024 * kItems) {
+    const size_t w0 = tile + (size_t)warp * (32 * kItems);
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
+      const size_t i = w0 + k * 32 + lane;
+      unsigned long long x = 0;
+      if (i < n) x = pow2 ? (sizes[i] + align - 1) & ~(unsigned long long)(align - 1) : (sizes[i] + align - 1) / align * align;
+      const int e = k * 32 + lane;
+      stage[e + (e >> 3)] = x;
+    }
+    __syncwarp();
+    unsigned long long v[kItems];
+    unsigned long long sum = 0;
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
+      v[k] = stage[lane * (kItems + 1) + k];
+      sum += v[k];
+    }
+    unsigned long long incl = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const unsigned long long o = __shfl_up_sync(kFull, incl, d);
@@ -276,11 +301,103 @@ place_kernel(const size_t* sizes, size_t* offsets, size_t n, unsigned long long*
       if (lane == 31) base_s = base + wi;
     }
     __syncthreads();
-    if (i < n) offsets[i] = base + warp_tot[warp] + (incl - v);
+    unsigned long long run = base + warp_tot[warp] + (incl - sum);
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
+      stage[lane * (kItems + 1) + k] = run;
+      run += v[k];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
+      const size_t i = w0 + k * 32 + lane;
+      const int e = k * 32 + lane;
+      if (i < n) offsets[i] = stage[e + (e >> 3)];
+    }
     base = base_s;
     __syncthreads();
   }
   if (threadIdx.x == 0) *cursor = base;
+}
+
+// Two-level placement for large waves (one CTA scanning 256 Ki sizes is latency-bound at ~0.2 ms):
+// per-tile sums -> place_kernel over the tile sums (cursor + header, as above) -> per-tile scan.
+constexpr int kPlaceTile = 256 * kPlaceItems; // chunks per CTA
+
+__device__ __forceinline__ unsigned long long padded_size(size_t x, size_t align, bool pow2)
+{
+  return pow2 ? (x + align - 1) & ~(unsigned long long)(align - 1) : (x + align - 1) / align * align;
+}
+
+__global__ void __launch_bounds__(256)
+place_sum_kernel(const size_t* sizes, size_t n, size_t align, size_t* tile_sum)
+{
+  __shared__ unsigned long long wsum[8];
+  const bool pow2 = (align & (align - 1)) == 0;
+  const size_t t0 = (size_t)blockIdx.x * kPlaceTile;
+  unsigned long long s = 0;
+#pragma unroll
+  for (int k = 0; k < kPlaceItems; ++k) {
+    const size_t i = t0 + (size_t)k * 256 + threadIdx.x;
+    if (i < n) s += padded_size(sizes[i], align, pow2);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(kFull, s, d);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += wsum[w];
+    tile_sum[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+place_scatter_kernel(const size_t* sizes, size_t* offsets, size_t n, size_t align, const size_t* tile_base)
+{
+  __shared__ unsigned long long stage_all[8 * kPlaceStage];
+  __shared__ unsigned long long warp_tot[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool pow2 = (align & (align - 1)) == 0;
+  unsigned long long* stage = stage_all + warp * kPlaceStage;
+  const size_t w0 = (size_t)blockIdx.x * kPlaceTile + (size_t)warp * (32 * kPlaceItems);
+#pragma unroll
+  for (int k = 0; k < kPlaceItems; ++k) {
+    const size_t i = w0 + k * 32 + lane;
+    const int e = k * 32 + lane;
+    stage[e + (e >> 3)] = i < n ? padded_size(sizes[i], align, pow2) : 0ull;
+  }
+  __syncwarp();
+  unsigned long long v[kPlaceItems];
+  unsigned long long sum = 0;
+#pragma unroll
+  for (int k = 0; k < kPlaceItems; ++k) {
+    v[k] = stage[lane * (kPlaceItems + 1) + k];
+    sum += v[k];
+  }
+  unsigned long long incl = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long o = __shfl_up_sync(kFull, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  unsigned long long run = tile_base[blockIdx.x] + (incl - sum);
+  for (int w = 0; w < warp; ++w) run += warp_tot[w];
+#pragma unroll
+  for (int k = 0; k < kPlaceItems; ++k) {
+    stage[lane * (kPlaceItems + 1) + k] = run;
+    run += v[k];
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < kPlaceItems; ++k) {
+    const size_t i = w0 + k * 32 + lane;
+    const int e = k * 32 + lane;
+    if (i < n) offsets[i] = stage[e + (e >> 3)];
+  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -345,6 +462,8 @@ public:
     if (chunk_ == 0) throw std::invalid_argument("hipcomp HLIF: uncompressed chunk size must be > 0");
     cu_check(cudaHostAlloc(reinterpret_cast<void**>(&header_host_), sizeof(CommonHeader) + 64, cudaHostAllocDefault),
              "cudaHostAlloc(header)");
+    cu_check(cudaFuncSetAttribute(place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlaceSmem),
+             "cudaFuncSetAttribute(place_kernel)");
   }
   ~BatchManager() override
   {
@@ -393,7 +512,7 @@ public:
     HeaderFill hf{header, format(), cfg.uncompressed_buffer_size, n, chunk_, (uint32_t)(data - comp_buffer)};
     unsigned long long* cursor = reinterpret_cast<unsigned long long*>(&header->comp_data_size);
     if (n == 0) {
-      place_kernel<<<1, 1024, 0, stream_>>>(sizes, offsets, 0, cursor, 1, hf);
+      place_kernel<<<1, 1024, kPlaceSmem, stream_>>>(sizes, offsets, 0, cursor, 1, hf);
       cu_check(cudaGetLastError(), "place_kernel");
       return;
     }
@@ -404,12 +523,21 @@ public:
     const void** in_ptrs = scratch_.reserve<const void*>(wave_);
     size_t* in_bytes = scratch_.reserve<size_t>(wave_);
     void** out_ptrs = scratch_.reserve<void*>(wave_);
+    size_t* tile_sum = scratch_.reserve<size_t>(wave_ / kPlaceTile + 1);
+    size_t* tile_base = scratch_.reserve<size_t>(wave_ / kPlaceTile + 1);
     for (size_t start = 0; start < n; start += wave_) {
       const size_t m = n - start < wave_ ? n - start : wave_;
       setup_compress_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(decomp_buffer, cfg.uncompressed_buffer_size, chunk_, start,
                                                                   m, slots, slot_stride_, in_ptrs, in_bytes, out_ptrs);
       batch_compress(in_ptrs, in_bytes, m, temp, temp_bytes, out_ptrs, sizes + start);
-      place_kernel<<<1, 1024, 0, stream_>>>(sizes + start, offsets + start, m, cursor, chunk_align(), hf);
+      if (m <= 8192) {
+        place_kernel<<<1, 1024, kPlaceSmem, stream_>>>(sizes + start, offsets + start, m, cursor, chunk_align(), hf);
+      } else {
+        const size_t tiles = (m + kPlaceTile - 1) / kPlaceTile;
+        place_sum_kernel<<<(int)tiles, 256, 0, stream_>>>(sizes + start, m, chunk_align(), tile_sum);
+        place_kernel<<<1, 1024, kPlaceSmem, stream_>>>(tile_sum, tile_base, tiles, cursor, 1, hf);
+        place_scatter_kernel<<<(int)tiles, 256, 0, stream_>>>(sizes + start, offsets + start, m, chunk_align(), tile_base);
+      }
       hf.header = nullptr;
       st_check(b200compGatherChunksAsync(out_ptrs, sizes + start, offsets + start, data, m, stream_), "gather");
     }
@@ -484,7 +612,7 @@ protected:
     dwave_ = 1u << 20;
     using W = b200comp::Workspace;
     const size_t comp_need = W::footprint<uint8_t>(wave_ * slot_stride_) + W::footprint<uint8_t>(comp_temp_bytes(wave_))
-                             + 3 * W::footprint<size_t>(wave_);
+                             + 3 * W::footprint<size_t>(wave_) + 2 * W::footprint<size_t>(wave_ / kPlaceTile + 1);
     const size_t decomp_need = 4 * W::footprint<size_t>(dwave_) + W::footprint<hipcompStatus_t>(dwave_);
     scratch_bytes_ = comp_need > decomp_need ? comp_need : decomp_need;
   }

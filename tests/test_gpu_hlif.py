@@ -208,3 +208,30 @@ def test_create_manager_rejects_unknown_format():
     buf[6] = 3  # GDeflate
     with pytest.raises(M.ManagerError):
         M.create_manager(buf)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,chunk,nbytes", [("cascaded", 4096, 10000 * 4096 + 1236), ("lz4", 4096, 9000 * 4096 + 77)])
+def test_large_wave_two_level_placement(kind, chunk, nbytes):
+    """Waves of more than 8192 chunks place their chunks with the two-level scan (hlif.cu place_sum / place_kernel /
+    place_scatter): offsets must be the exclusive sum of the padded sizes, gapless, and the container must round-trip."""
+    raw = make_data(kind, nbytes, 99)
+    mgr = make_manager(kind, chunk)
+    d_raw = torch.from_numpy(raw).cuda()
+    cc = mgr.configure_compression(nbytes)
+    assert cc.num_chunks > 8192
+    comp = torch.zeros(cc.max_compressed_buffer_size, dtype=torch.uint8, device="cuda")
+    mgr.compress(d_raw, comp, cc)
+    total = mgr.get_compressed_output_size(comp)
+    blob = comp[:total].cpu().numpy().tobytes()
+    hdr, _ = parse_container(blob, kind)
+    align = 8 if kind == "cascaded" else 1
+    padded = (hdr["sizes"].astype(np.int64) + align - 1) // align * align
+    expect = np.cumsum(padded) - padded
+    assert np.array_equal(hdr["offsets"].astype(np.int64), expect)
+    assert hdr["comp_data_size"] == int(padded.sum()) and total == hdr["comp_data_offset"] + int(padded.sum())
+    dc = mgr.configure_decompression(comp)
+    back = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    mgr.decompress(back, comp, dc)
+    torch.cuda.synchronize()
+    assert dc.get_status() == 0 and torch.equal(back, d_raw)
