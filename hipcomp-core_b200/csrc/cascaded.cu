@@ -678,9 +678,9 @@ __device__ void raw_copy(const T* in, size_t n, uint8_t* out)
 // only the compacted (run value, run end) pairs go to shared memory.  One striped pass then turns
 // ends into lengths and values into deltas, in place, in the swizzled layout write_array packs from.
 // Returns false when the chunk does not fit (caller falls back to the raw partition).
-template <typename T>
-__device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, size_t limit, bool use_bp, T* A,
-                                    uint16_t* C, int R)
+template <typename T, int R>
+__device__ bool compress_chunk_rd1(const T* src, uint8_t* out, size_t& cur, size_t limit, bool use_bp, T* A,
+                                   uint16_t* C)
 {
   static_assert(sizeof(T) == 4, "fast path is for 4-byte elements");
   constexpr int N = kChunkBytes / 4;
@@ -791,7 +791,7 @@ __device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, siz
   __syncwarp();
 
   uint32_t ob_counts, ob_vals;
-  if (R == 2) {
+  if constexpr (R == 2) {
     // num_RLEs = 2 (the library's default option set): the first RLE + delta above are shared; the
     // deltas then take the generic second run-length layer.  Same calls, same order, same bytes as the
     // layer loop of compress_partition.
@@ -861,7 +861,7 @@ __device__ bool compress_chunk_r1d1(const T* src, uint8_t* out, size_t& cur, siz
 }
 
 // One warp compresses one partition.  (reference do_cascaded_compression_kernel :761-1058)
-template <typename T>
+template <typename T, bool kR2>
 __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, size_t* comp_bytes_out, int type_id,
                                    int R, int D, int bp, uint8_t* smem)
 {
@@ -885,12 +885,13 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
   size_t cur = 8;
   const int layers = R > D ? R : D;
 
-  const bool fast_r1d1 = W == 4 && (R == 1 || R == 2) && D == 1 && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
+  const bool fast_r1d1 = W == 4 && (kR2 ? R == 2 : R == 1) && D == 1 && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
 
   for (size_t c = 0; c < n_chunks && use_compression; ++c) {
     if constexpr (sizeof(T) == 4) {
       if (fast_r1d1 && n_total - c * N >= (size_t)N) {
-        if (!compress_chunk_r1d1<T>(in + c * N, out, cur, limit, bp != 0, A, C, R)) use_compression = false;
+        const bool fits = compress_chunk_rd1<T, kR2 ? 2 : 1>(in + c * N, out, cur, limit, bp != 0, A, C);
+        if (!fits) use_compression = false;
         continue;
       }
     }
@@ -955,7 +956,10 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
   }
 }
 
-template <typename T>
+// kR2: the instantiation launched for num_RLEs = 2, num_deltas = 1 (the library's default option set).  It is a
+// separate kernel because the second run-length layer, when it shares a function with the R = 1 fast path, costs
+// that path 3 % (2570 -> 2498 GB/s on C3) through register allocation alone; the host knows R at launch.
+template <typename T, bool kR2>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, B200_CASC_COMP_MINB)
 compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
                 size_t batch, int type_id, int R, int D, int bp)
@@ -965,7 +969,7 @@ compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const*
   uint8_t* smem = smem_raw + (size_t)warp * CompSmem<T>::BYTES;
   const size_t stride = (size_t)gridDim.x * kWarpsPerCta;
   for (size_t p = (size_t)blockIdx.x * kWarpsPerCta + warp; p < batch; p += stride) {
-    compress_partition<T>(static_cast<const T*>(in_ptrs[p]), in_bytes[p], static_cast<uint8_t*>(out_ptrs[p]),
+    compress_partition<T, kR2>(static_cast<const T*>(in_ptrs[p]), in_bytes[p], static_cast<uint8_t*>(out_ptrs[p]),
                           out_bytes + p, type_id, R, D, bp, smem);
     __syncwarp();
   }
@@ -1105,101 +1109,6 @@ __device__ bool decompress_chunk_r1d1(const uint8_t* chunk_ptr, uint32_t avail_w
   return true;
 }
 
-// Tail of the decoder shared by every option set that ends in (first RLE, one delta), e.g. the library default
-// num_RLEs = 2: the generic layers have left the nv deltas of the first layer in A (swizzled shared memory);
-// the bit-packed first-layer run lengths are read straight from the compressed chunk.  Same scheme as
-// decompress_chunk_r1d1: deltas are added onto the run starts of a zeroed array O, one register prefix sum
-// produces the 1024 outputs.  O must not alias A.  Returns false before writing anything to global memory
-// when a precondition fails (the generic layers then continue from the untouched A).
-template <typename T>
-__device__ bool decompress_tail_d1(const uint8_t* counts_ptr, uint32_t cb, const T* A, int nv, T seed, T* gout,
-                                   uint32_t* O)
-{
-  static_assert(sizeof(T) == 4, "4-byte elements");
-  constexpr uint32_t N = kChunkBytes / 4;
-  const int lane = lane_id();
-  if (cb < 8 || (cb & 3)) return false;
-  const uint32_t* cw = reinterpret_cast<const uint32_t*>(counts_ptr);
-  const uint32_t cfr = __ldg(cw), cmeta = __ldg(cw + 1);
-  const uint32_t cbw = cmeta >> 16, nc = cmeta & 0xffffu;
-  const int m = nv + 1;
-  if (nc > N || cbw > 16 || (uint32_t)m > N || nc < (uint32_t)m) return false;
-  if (8u + 4u * ((nc * cbw + 31u) >> 5) > cb) return false;
-  const uint32_t cmask = (1u << cbw) - 1u;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) reinterpret_cast<uint4*>(O)[lane + 32 * k] = make_uint4(0, 0, 0, 0);
-  __syncwarp();
-  uint32_t carry = 0;
-  for (int u = 0; u * 64 < m; ++u) {
-    const int r0 = 64 * u + lane, r1 = r0 + 32;
-    uint32_t len0 = 0, len1 = 0;
-    T d0 = 0, d1 = 0;
-    if (r0 < m) {
-      const uint32_t cp = (uint32_t)r0 * cbw;
-      // the word after the last packed word is inside the chunk (the next array's header follows)
-      const uint32_t cv = __funnelshift_r(__ldg(cw + 2 + (cp >> 5)), __ldg(cw + 3 + (cp >> 5)), cp & 31) & cmask;
-      len0 = (uint32_t)(uint16_t)(cv + cfr);
-      d0 = r0 == 0 ? seed : A[Swz<T>::p(r0 - 1)];
-    }
-    if (r1 < m) {
-      const uint32_t cp = (uint32_t)r1 * cbw;
-      const uint32_t cv = __funnelshift_r(__ldg(cw + 2 + (cp >> 5)), __ldg(cw + 3 + (cp >> 5)), cp & 31) & cmask;
-      len1 = (uint32_t)(uint16_t)(cv + cfr);
-      d1 = A[Swz<T>::p(r1 - 1)];
-    }
-    if (__any_sync(kFull, len0 > N || len1 > N)) return false;
-    const uint32_t packed = len0 | (len1 << 16);
-    uint32_t incl = packed;
-#pragma unroll
-    for (int dd = 1; dd < 32; dd <<= 1) {
-      const uint32_t o = __shfl_up_sync(kFull, incl, dd);
-      if (lane >= dd) incl += o;
-    }
-    const uint32_t tot = __shfl_sync(kFull, incl, 31);
-    const uint32_t ex = incl - packed;
-    const uint32_t start0 = carry + (ex & 0xffffu);
-    const uint32_t start1 = carry + (tot & 0xffffu) + (ex >> 16);
-    carry += (tot & 0xffffu) + (tot >> 16);
-    if (r0 < m && start0 < N) atomicAdd(O + start0, (uint32_t)d0);
-    if (r1 < m && start1 < N) atomicAdd(O + start1, (uint32_t)d1);
-  }
-  if (carry != N) return false;
-  __syncwarp();
-  const uint4* O4 = reinterpret_cast<const uint4*>(O);
-  uint4 q[8];
-  uint32_t sc[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    q[k] = O4[lane + 32 * k];
-    q[k].y += q[k].x;
-    q[k].z += q[k].y;
-    q[k].w += q[k].z;
-    sc[k] = q[k].w;
-  }
-#pragma unroll
-  for (int dd = 1; dd < 32; dd <<= 1) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const uint32_t o = __shfl_up_sync(kFull, sc[k], dd);
-      if (lane >= dd) sc[k] += o;
-    }
-  }
-  uint32_t tile_base = 0;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const uint32_t tot = __shfl_sync(kFull, sc[k], 31);
-    const uint32_t ex = sc[k] - q[k].w + tile_base;
-    q[k].x += ex;
-    q[k].y += ex;
-    q[k].z += ex;
-    q[k].w += ex;
-    tile_base += tot;
-    st_stream16(reinterpret_cast<uint4*>(gout) + lane + 32 * k, q[k]);
-  }
-  __syncwarp();
-  return true;
-}
-
 // One warp decompresses one partition.  (reference cascaded_decompression_fcn :1106-1435)
 template <typename T>
 __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* out, size_t out_cap,
@@ -1276,24 +1185,6 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
       // exact reverse of the encoder's layer order R1 D1 R2 D2 ... (see DESIGN.md on
       // the reference's interleaving rule for num_deltas > num_RLEs)
       for (int l = layers - 1; l >= 0 && ok; --l) {
-        if constexpr (sizeof(T) == 4) {
-          // last two layers (delta, first RLE) fused for full, aligned chunks
-          if (l == 0 && D == 1 && R >= 1 && bp != 0 && n + 1 <= N && n_total - done >= (size_t)N &&
-              (reinterpret_cast<uintptr_t>(out + done) & 15) == 0) {
-            const uint32_t cb = __ldg(mw + 1);
-            const size_t cpos = arrays + off[0];
-            if (cpos + ((cb + 3u) & ~3u) <= end) {
-              const T seed = *reinterpret_cast<const T*>(comp + chunk + delta_off);
-              __syncwarp();
-              if (decompress_tail_d1<T>(comp + cpos, cb, A, n, seed, out + done, reinterpret_cast<uint32_t*>(C))) {
-                n = N;
-                wrote_global = true;
-                break;
-              }
-              __syncwarp();
-            }
-          }
-        }
         if (l < D) {
           if (n + 1 > N) { ok = false; break; }
           const T seed = *reinterpret_cast<const T*>(comp + chunk + delta_off + l * W);
@@ -1398,10 +1289,17 @@ static hipcompStatus_t launch_compress(const void* const* in_ptrs, const size_t*
                                        cudaStream_t stream)
 {
   constexpr int smem = CompSmem<T>::BYTES * kWarpsPerCta;
-  allow_smem(compress_kernel<T>, smem); // per device, so not cached in a static
   const int per_sm = (227 * 1024) / (smem + 1024);
-  compress_kernel<T><<<grid_for(batch, per_sm < 16 ? per_sm : 16), kWarpsPerCta * 32, smem, stream>>>(
-      in_ptrs, in_bytes, out_ptrs, out_bytes, batch, (int)o.type, o.num_RLEs, o.num_deltas, o.use_bp);
+  const int grid = grid_for(batch, per_sm < 16 ? per_sm : 16);
+  if (sizeof(T) == 4 && o.num_RLEs == 2 && o.num_deltas == 1) {
+    allow_smem(compress_kernel<T, true>, smem); // per device, so not cached in a static
+    compress_kernel<T, true><<<grid, kWarpsPerCta * 32, smem, stream>>>(
+        in_ptrs, in_bytes, out_ptrs, out_bytes, batch, (int)o.type, o.num_RLEs, o.num_deltas, o.use_bp);
+  } else {
+    allow_smem(compress_kernel<T, false>, smem);
+    compress_kernel<T, false><<<grid, kWarpsPerCta * 32, smem, stream>>>(
+        in_ptrs, in_bytes, out_ptrs, out_bytes, batch, (int)o.type, o.num_RLEs, o.num_deltas, o.use_bp);
+  }
   return check_launch("hipcompBatchedCascadedCompressAsync()");
 }
 
