@@ -1109,8 +1109,103 @@ __device__ bool decompress_chunk_r1d1(const uint8_t* chunk_ptr, uint32_t avail_w
   return true;
 }
 
-// One warp decompresses one partition.  (reference cascaded_decompression_fcn :1106-1435)
+// Tail of the decoder shared by every option set that ends in (first RLE, one delta), e.g. the library default
+// num_RLEs = 2: the generic layers have left the nv deltas of the first layer in A (swizzled shared memory);
+// the bit-packed first-layer run lengths are read straight from the compressed chunk.  Same scheme as
+// decompress_chunk_r1d1: deltas are added onto the run starts of a zeroed array O, one register prefix sum
+// produces the 1024 outputs.  O must not alias A.  Returns false before writing anything to global memory
+// when a precondition fails (the generic layers then continue from the untouched A).
 template <typename T>
+__device__ bool decompress_tail_d1(const uint8_t* counts_ptr, uint32_t cb, const T* A, int nv, T seed, T* gout,
+                                   uint32_t* O)
+{
+  static_assert(sizeof(T) == 4, "4-byte elements");
+  constexpr uint32_t N = kChunkBytes / 4;
+  const int lane = lane_id();
+  if (cb < 8 || (cb & 3)) return false;
+  const uint32_t* cw = reinterpret_cast<const uint32_t*>(counts_ptr);
+  const uint32_t cfr = __ldg(cw), cmeta = __ldg(cw + 1);
+  const uint32_t cbw = cmeta >> 16, nc = cmeta & 0xffffu;
+  const int m = nv + 1;
+  if (nc > N || cbw > 16 || (uint32_t)m > N || nc < (uint32_t)m) return false;
+  if (8u + 4u * ((nc * cbw + 31u) >> 5) > cb) return false;
+  const uint32_t cmask = (1u << cbw) - 1u;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) reinterpret_cast<uint4*>(O)[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+  __syncwarp();
+  uint32_t carry = 0;
+  for (int u = 0; u * 64 < m; ++u) {
+    const int r0 = 64 * u + lane, r1 = r0 + 32;
+    uint32_t len0 = 0, len1 = 0;
+    T d0 = 0, d1 = 0;
+    if (r0 < m) {
+      const uint32_t cp = (uint32_t)r0 * cbw;
+      // the word after the last packed word is inside the chunk (the next array's header follows)
+      const uint32_t cv = __funnelshift_r(__ldg(cw + 2 + (cp >> 5)), __ldg(cw + 3 + (cp >> 5)), cp & 31) & cmask;
+      len0 = (uint32_t)(uint16_t)(cv + cfr);
+      d0 = r0 == 0 ? seed : A[Swz<T>::p(r0 - 1)];
+    }
+    if (r1 < m) {
+      const uint32_t cp = (uint32_t)r1 * cbw;
+      const uint32_t cv = __funnelshift_r(__ldg(cw + 2 + (cp >> 5)), __ldg(cw + 3 + (cp >> 5)), cp & 31) & cmask;
+      len1 = (uint32_t)(uint16_t)(cv + cfr);
+      d1 = A[Swz<T>::p(r1 - 1)];
+    }
+    if (__any_sync(kFull, len0 > N || len1 > N)) return false;
+    const uint32_t packed = len0 | (len1 << 16);
+    uint32_t incl = packed;
+#pragma unroll
+    for (int dd = 1; dd < 32; dd <<= 1) {
+      const uint32_t o = __shfl_up_sync(kFull, incl, dd);
+      if (lane >= dd) incl += o;
+    }
+    const uint32_t tot = __shfl_sync(kFull, incl, 31);
+    const uint32_t ex = incl - packed;
+    const uint32_t start0 = carry + (ex & 0xffffu);
+    const uint32_t start1 = carry + (tot & 0xffffu) + (ex >> 16);
+    carry += (tot & 0xffffu) + (tot >> 16);
+    if (r0 < m && start0 < N) atomicAdd(O + start0, (uint32_t)d0);
+    if (r1 < m && start1 < N) atomicAdd(O + start1, (uint32_t)d1);
+  }
+  if (carry != N) return false;
+  __syncwarp();
+  const uint4* O4 = reinterpret_cast<const uint4*>(O);
+  uint4 q[8];
+  uint32_t sc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    q[k] = O4[lane + 32 * k];
+    q[k].y += q[k].x;
+    q[k].z += q[k].y;
+    q[k].w += q[k].z;
+    sc[k] = q[k].w;
+  }
+#pragma unroll
+  for (int dd = 1; dd < 32; dd <<= 1) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t o = __shfl_up_sync(kFull, sc[k], dd);
+      if (lane >= dd) sc[k] += o;
+    }
+  }
+  uint32_t tile_base = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t tot = __shfl_sync(kFull, sc[k], 31);
+    const uint32_t ex = sc[k] - q[k].w + tile_base;
+    q[k].x += ex;
+    q[k].y += ex;
+    q[k].z += ex;
+    q[k].w += ex;
+    tile_base += tot;
+    st_stream16(reinterpret_cast<uint4*>(gout) + lane + 32 * k, q[k]);
+  }
+  __syncwarp();
+  return true;
+}
+
+// One warp decompresses one partition.  (reference cascaded_decompression_fcn :1106-1435)
+template <typename T, bool kTail>
 __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* out, size_t out_cap,
                                      size_t* actual_out, hipcompStatus_t* status_out, uint8_t* smem)
 {
@@ -1185,6 +1280,24 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
       // exact reverse of the encoder's layer order R1 D1 R2 D2 ... (see DESIGN.md on
       // the reference's interleaving rule for num_deltas > num_RLEs)
       for (int l = layers - 1; l >= 0 && ok; --l) {
+        if constexpr (kTail && sizeof(T) == 4) {
+          // last two layers (delta, first RLE) fused for full, aligned chunks
+          if (l == 0 && D == 1 && R >= 1 && bp != 0 && n + 1 <= N && n_total - done >= (size_t)N &&
+              (reinterpret_cast<uintptr_t>(out + done) & 15) == 0) {
+            const uint32_t cb = __ldg(mw + 1);
+            const size_t cpos = arrays + off[0];
+            if (cpos + ((cb + 3u) & ~3u) <= end) {
+              const T seed = *reinterpret_cast<const T*>(comp + chunk + delta_off);
+              __syncwarp();
+              if (decompress_tail_d1<T>(comp + cpos, cb, A, n, seed, out + done, reinterpret_cast<uint32_t*>(C))) {
+                n = N;
+                wrote_global = true;
+                break;
+              }
+              __syncwarp();
+            }
+          }
+        }
         if (l < D) {
           if (n + 1 > N) { ok = false; break; }
           const T seed = *reinterpret_cast<const T*>(comp + chunk + delta_off + l * W);
@@ -1235,8 +1348,11 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
 }
 // The element width of the whole batch comes from partition 0's type byte, as in
 // the reference (CascadedBatch.hip:156-168).  One launch per width; the three
-// that do not match return after one load.
-template <typename T>
+// that do not match return after one load.  For 4-byte elements there are two instantiations, selected the same
+// way from partition 0's header: kTail (num_RLEs >= 2, num_deltas = 1 - the library's default option set) fuses
+// the last two layers behind the generic ones; keeping it out of the other instantiation keeps that one's
+// register allocation (80 regs, no spills) for the headline R = 1 fast path.  Both decode any partition.
+template <typename T, bool kTail>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, void* const* out_ptrs,
                   const size_t* out_caps, size_t* actual, hipcompStatus_t* statuses, size_t batch)
@@ -1253,12 +1369,16 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, void* 
   default: width = 1; break; // unknown type byte: the 1-byte instantiation reports the errors
   }
   if (width != (int)sizeof(T)) return;
+  if (sizeof(T) == 4) {
+    const bool tail_batch = p0[0] >= 2 && p0[1] == 1 && p0[2] != 0; // num_RLEs, num_deltas, use_bp of partition 0
+    if (tail_batch != kTail) return;
+  }
   const int warp = threadIdx.x >> 5;
   uint8_t* smem = smem_raw + (size_t)warp * DecompSmem<T>::BYTES;
   const size_t stride = (size_t)gridDim.x * kWarpsPerCta;
   for (size_t p = (size_t)blockIdx.x * kWarpsPerCta + warp; p < batch; p += stride) {
     const bool known = type_id >= 0 && type_id <= 7;
-    decompress_partition<T>(known ? static_cast<const uint8_t*>(comp_ptrs[p]) : nullptr, comp_bytes[p],
+    decompress_partition<T, kTail>(known ? static_cast<const uint8_t*>(comp_ptrs[p]) : nullptr, comp_bytes[p],
                             static_cast<T*>(out_ptrs[p]), out_caps[p], actual ? actual + p : nullptr,
                             statuses ? statuses + p : nullptr, smem);
     __syncwarp();
@@ -1309,10 +1429,16 @@ static hipcompStatus_t launch_decompress(const void* const* comp_ptrs, const siz
                                          hipcompStatus_t* statuses, size_t batch, cudaStream_t stream)
 {
   constexpr int smem = DecompSmem<T>::BYTES * kWarpsPerCta;
-  allow_smem(decompress_kernel<T>, smem);
+  allow_smem(decompress_kernel<T, false>, smem);
   const int per_sm = (227 * 1024) / (smem + 1024);
-  decompress_kernel<T><<<grid_for(batch, per_sm < 16 ? per_sm : 16), kWarpsPerCta * 32, smem, stream>>>(
-      comp_ptrs, comp_bytes, out_ptrs, out_caps, actual, statuses, batch);
+  const int grid = grid_for(batch, per_sm < 16 ? per_sm : 16);
+  decompress_kernel<T, false><<<grid, kWarpsPerCta * 32, smem, stream>>>(comp_ptrs, comp_bytes, out_ptrs, out_caps,
+                                                                        actual, statuses, batch);
+  if (sizeof(T) == 4) {
+    allow_smem(decompress_kernel<T, true>, smem);
+    decompress_kernel<T, true><<<grid, kWarpsPerCta * 32, smem, stream>>>(comp_ptrs, comp_bytes, out_ptrs, out_caps,
+                                                                         actual, statuses, batch);
+  }
   return check_launch("hipcompBatchedCascadedDecompressAsync()");
 }
 
