@@ -172,12 +172,31 @@ class CpuCodec:
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    # The sampler is started BEFORE the warm-up steps (nvidia-smi needs up to a second to produce its first line
+    # on an 8-GPU box, longer than a short timed region) and stop() keeps the samples whose timestamp falls
+    # inside the timed window [mark_begin, mark_end]; if the window is shorter than the sampling period it
+    # falls back to the samples taken under the same load during warm-up and says so in "window".
+    FIELDS = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
         self.idx, self.proc = gpu_index, None
+        self.t0 = self.t1 = None
+
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
+
+    @staticmethod
+    def _stamp(text):
+        import datetime
+        try:
+            return datetime.datetime.strptime(text.strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+        except ValueError:
+            return None
 
     def start(self):
         try:
@@ -197,22 +216,27 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
             out = ""
-        sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []
         for line in out.splitlines():
             f = [x.strip() for x in line.split(",")]
             if len(f) < 8:
                 continue
             try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
+                rows.append((self._stamp(f[0]), float(f[1]), float(f[2]),
+                             {nme for nme, v in zip(names, f[4:8]) if v.lower().startswith("active")}))
             except ValueError:
                 continue
-            for nme, v in zip(names, f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(nme)
+        window = "timed region"
+        inside = [r for r in rows if r[0] is not None and self.t0 is not None and self.t1 is not None
+                  and self.t0 - 0.05 <= r[0] <= self.t1 + 0.05]
+        if not inside:
+            inside, window = rows, "warm-up + timed region (timed region shorter than the sampling period)"
+        sm = [r[1] for r in inside]
+        mx = [r[2] for r in inside]
+        reasons = set().union(*[r[3] for r in inside]) if inside else set()
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 # ----------------------------------------------------------------------------- GPU arm
@@ -372,6 +396,8 @@ def run_b200(args):
     plan = Plan(args.codec, raw, wl["chunk"], casc_opts)
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
+    clocks = ClockSampler(local)
+    clocks.start()
     for _ in range(max(args.warmup, 3)):
         plan.compress()
         plan.decompress()
@@ -380,10 +406,9 @@ def run_b200(args):
 
     # ---- timed region: K steps, inputs resident in HBM.  1 GiB input + ~1.4 GiB of other buffers per
     # step is far larger than the 126 MB L2, so nothing survives in L2 from one step to the next.
-    clocks = ClockSampler(local)
     barrier(world)
     torch.cuda.synchronize()
-    clocks.start()
+    clocks.mark_begin()
     marks = []
     for _ in range(args.steps):
         e0, e1, e2 = ev(), ev(), ev()
@@ -394,6 +419,7 @@ def run_b200(args):
         e2.record()
         marks.append((e0, e1, e2))
     torch.cuda.synchronize()
+    clocks.mark_end()
     barrier(world)
     clk = clocks.stop()
     t_comp = sum(a.elapsed_time(b) for a, b, _ in marks) / 1e3
