@@ -1,15 +1,17 @@
 // b200comp — batched LZ4 block codec for sm_100a.
 //
-// C ABI replaces reference src/lowlevel/LZ4Batch.cpp:71-224; the encoder keeps the
-// reference's greedy match policy (src/LZ4Kernels.hiph:793-969: 32-position
-// window, intra-window twins, uint16 hash table with last-lane-wins insertion) so
-// that its output is the same byte stream, and changes the data movement: the
-// hash table lives in shared memory (the reference keeps 32 KiB per chunk in
-// global memory and re-initialises it through L2), window keys come from two
-// aligned word loads + funnel shift instead of byte loads and shuffles, and
-// literal runs move as 16-byte vectors.  The decoder bounds every compressed
-// read (the reference's does not).
+// C ABI replaces reference src/lowlevel/LZ4Batch.cpp:71-224.
+//
+// Encoders.  Chunks up to 64 KiB (every headline configuration) go to the team encoder of
+// lz4_team.cuh: one CTA per chunk, chunk and hash table resident in shared memory, all
+// positions matched in parallel.  Its streams are plain LZ4 blocks with a ratio at or above the
+// reference's, but not the reference's bytes.  Larger chunks (up to the format's 16 MiB) keep
+// the one-warp-per-chunk kernel below, which reproduces the reference's greedy policy
+// (src/LZ4Kernels.hiph:793-969: 32-position window, intra-window twins, uint16 hash table in
+// the caller's workspace, last-lane-wins insertion) byte for byte.
+// The decoder bounds every compressed read (the reference's does not).
 #include "lz_common.cuh"
+#include "lz4_team.cuh"
 #include "lz_pipeline.cuh"
 
 #include <cstdlib>
@@ -722,6 +724,32 @@ __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_byt
   }
 }
 
+// ---- team encoder launch (lz4_team.cuh).  Hash-table bits and team width by declared chunk size;
+//      oracle/lz4_team_model.c is called with the same hash_log by the tests.
+constexpr size_t kTeamMaxChunk = 65536;
+
+template <int CAP, int HL, int W>
+static void launch_team_cfg(const void* const* in_ptrs, const size_t* in_bytes, size_t batch, void* const* out_ptrs,
+                            size_t* out_bytes, cudaStream_t stream, int ctas_per_sm)
+{
+  using L = TeamLayout<CAP, HL, W>;
+  allow_smem(compress_team_kernel<CAP, HL, W>, (int)L::kBytes);
+  const size_t cap = (size_t)sm_count() * ctas_per_sm;
+  const int grid = (int)(batch < cap ? batch : cap);
+  compress_team_kernel<CAP, HL, W><<<grid, W * 32, L::kBytes, stream>>>(in_ptrs, in_bytes, out_ptrs, out_bytes, batch);
+}
+
+static void launch_team(const void* const* in_ptrs, const size_t* in_bytes, size_t max_chunk, size_t batch,
+                        void* const* out_ptrs, size_t* out_bytes, cudaStream_t stream)
+{
+  if (max_chunk <= 4096)
+    launch_team_cfg<4096, 12, 4>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 6);
+  else if (max_chunk <= 16384)
+    launch_team_cfg<16384, 13, 8>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 3);
+  else
+    launch_team_cfg<65536, 14, 8>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 2);
+}
+
 } // namespace lz4
 } // namespace b200comp
 
@@ -774,6 +802,24 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  switch (format_opts.data_type) {
+  case HIPCOMP_TYPE_BITS:
+  case HIPCOMP_TYPE_CHAR:
+  case HIPCOMP_TYPE_UCHAR:
+  case HIPCOMP_TYPE_SHORT:
+  case HIPCOMP_TYPE_USHORT:
+  case HIPCOMP_TYPE_INT:
+  case HIPCOMP_TYPE_UINT:
+    break;
+  default:
+    return fail(hipcompErrorInvalidValue, fn, "Unsupported input data type");
+  }
+  if (max_uncompressed_chunk_bytes <= lz4::kTeamMaxChunk) {
+    // byte-granular matching for every data type: a superset of the element-granular matches
+    lz4::launch_team(device_uncompressed_ptrs, device_uncompressed_bytes, max_uncompressed_chunk_bytes,
+                     batch_size, device_compressed_ptrs, device_compressed_bytes, stream);
+    return check_launch(fn);
+  }
   const bool global_table = (size_t)ht * sizeof(uint16_t) > 8192;
   if (global_table && device_temp_ptr == nullptr)
     return fail(hipcompErrorInvalidValue, fn, "'device_temp_ptr' must not be null.");

@@ -19,7 +19,8 @@ CANNOT_DECOMPRESS = 12
 
 
 def build():
-    srcs = [os.path.join(_ORACLE_DIR, f) for f in ("cascaded_oracle.c", "lz4_oracle.c", "snappy_oracle.c")]
+    srcs = [os.path.join(_ORACLE_DIR, f)
+            for f in ("cascaded_oracle.c", "lz4_oracle.c", "snappy_oracle.c", "lz4_team_model.c", "Makefile")]
     if os.path.exists(_SO) and all(os.path.getmtime(_SO) >= os.path.getmtime(s) for s in srcs):
         return _SO
     subprocess.check_call(["make", "-C", _ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
@@ -49,6 +50,8 @@ def lib():
         L.lz4_oracle_compress.argtypes = [vp, sz, vp, C.c_int, C.c_uint32]
         L.lz4_oracle_decompress.restype = C.c_int
         L.lz4_oracle_decompress.argtypes = [vp, sz, vp, sz, C.c_int, C.POINTER(sz)]
+        L.lz4_team_model_compress.restype = sz
+        L.lz4_team_model_compress.argtypes = [vp, sz, vp, C.c_int]
         L.snappy_oracle_max_compressed.restype = sz
         L.snappy_oracle_max_compressed.argtypes = [sz]
         L.snappy_oracle_compress.restype = sz
@@ -109,6 +112,27 @@ def lz4_compress(data, tsize=1, max_chunk=None):
     out = np.zeros(lz4_max_compressed(len(a)) + 16, dtype=np.uint8)
     n = lib().lz4_oracle_compress(_p(a), len(a), _p(out), tsize, ht)
     return out[:n].copy()
+
+
+def lz4_team_hash_log(max_chunk):
+    """Hash-table bits the team encoder uses for a declared maximum chunk size (csrc/lz4.cu launch_team)."""
+    return 12 if max_chunk <= 4096 else 13 if max_chunk <= 16384 else 14
+
+
+def lz4_team_compress(data, max_chunk=None):
+    """b200comp's own encoder policy for chunks <= 64 KiB (oracle/lz4_team_model.c)."""
+    a = _buf(data)
+    assert len(a) <= 65536
+    out = np.zeros(lz4_max_compressed(len(a)) + 16, dtype=np.uint8)
+    n = lib().lz4_team_model_compress(_p(a), len(a), _p(out), lz4_team_hash_log(max_chunk or max(len(a), 1)))
+    return out[:n].copy()
+
+
+def lz4_product_compress(data, tsize=1, max_chunk=None):
+    """The stream libhipcomp.so is expected to produce: team policy up to 64 KiB declared chunk size,
+    the reference's policy above."""
+    mc = max_chunk if max_chunk is not None else max(len(_buf(data)), 1)
+    return lz4_team_compress(data, mc) if mc <= 65536 else lz4_compress(data, tsize, mc)
 
 
 def lz4_decompress(comp, cap, write_output=True):

@@ -63,7 +63,7 @@ def parse_container(blob, kind):
 
 def oracle_encode(kind, chunk, opts=None, max_chunk=None):
     if kind == "lz4":
-        return o.lz4_compress(chunk, 1, max_chunk)
+        return o.lz4_product_compress(chunk, 1, max_chunk)
     if kind == "snappy":
         return o.snappy_compress(chunk)
     return o.casc_compress(chunk, opts.type, opts.num_RLEs, opts.num_deltas, opts.use_bp)

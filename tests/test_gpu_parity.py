@@ -27,17 +27,45 @@ def ragged_chunks(max_size, n, seed):
 
 # ------------------------------------------------------------------ LZ4
 @pytest.mark.parametrize("tsize,type_id", [(1, 0), (1, 0xFF), (2, 3), (4, 4)])
-@pytest.mark.parametrize("max_chunk", [4096, 65536])
-def test_lz4_bit_exact_with_oracle(tsize, type_id, max_chunk):
+@pytest.mark.parametrize("max_chunk", [4096, 16384, 65536])
+def test_lz4_team_encoder_bit_exact_with_model(tsize, type_id, max_chunk):
+    """Chunks <= 64 KiB: the stream is byte-identical to the sequential statement of our own policy
+    (oracle/lz4_team_model.c), decodes with liblz4 and with the reference-policy oracle decoder, and is never
+    larger than GetMaxOutputChunkSize."""
+    from test_oracle_lz4 import stock_decompress
+
     g = _g()
     chunks = [c[: len(c) // tsize * tsize] for c in ragged_chunks(max_chunk, 48, 1000 + max_chunk + tsize)]
     chunks += datagen.mixed_chunks(max_chunk, 12, 77)
     comp, dec, status, sizes, actual = g.roundtrip("lz4", chunks, opts=g.L.LZ4Opts(type_id), max_chunk=max_chunk)
     for i, c in enumerate(chunks):
-        exp = o.lz4_compress(c, tsize, max_chunk)
+        exp = o.lz4_team_compress(c, max_chunk)
         assert comp[i].tobytes() == exp.tobytes(), f"chunk {i} (len {len(c)}) compressed stream differs"
+        assert len(comp[i]) <= o.lz4_max_compressed(max_chunk)
         assert status[i] == 0 and sizes[i] == len(c) and actual[i] == len(c)
         assert dec[i].tobytes() == c.tobytes()
+        if len(c):
+            n, out = stock_decompress(comp[i], len(c))
+            assert n == len(c) and out.tobytes() == c.tobytes()
+
+
+@pytest.mark.parametrize("kind", ["logs", "text", "ints", "zeros", "random", "line37"])
+def test_lz4_team_encoder_ratio_vs_reference_policy(kind):
+    """North star: compression ratio within 1 % of the reference encoder on every input class.  The reference
+    policy is oracle/lz4_oracle.c (byte-identical to the reference GPU encoder, tests/test_gpu_reference.py)."""
+    g = _g()
+    n, cb = 2 << 20, 65536
+    rng = np.random.default_rng(11)
+    raw = {"logs": lambda: datagen.log_lines(n, 21), "text": lambda: datagen.zipf_text(n, 22),
+           "ints": lambda: datagen.sorted_ints(n // 4, 23).view(np.uint8), "zeros": lambda: np.zeros(n, np.uint8),
+           "random": lambda: rng.integers(0, 256, n, dtype=np.uint8),
+           "line37": lambda: np.frombuffer((b"the quick brown fox jumps over a dog\n" * (n // 37 + 1))[:n], np.uint8)}[kind]()
+    chunks = [raw[i : i + cb] for i in range(0, n, cb)]
+    comp, dec, status, sizes, actual = g.roundtrip("lz4", chunks, max_chunk=cb)
+    ours = sum(len(c) for c in comp)
+    ref = sum(len(o.lz4_compress(c, 1, cb)) for c in chunks)
+    assert all(d.tobytes() == c.tobytes() for d, c in zip(dec, chunks)) and (status == 0).all()
+    assert n / ours >= 0.99 * (n / ref), f"{kind}: ratio {n / ours:.4f} vs reference policy {n / ref:.4f}"
 
 
 def test_lz4_decodes_liblz4_streams():
@@ -57,6 +85,7 @@ def test_lz4_large_chunk_and_null_outputs():
     chunks = [datagen.log_lines(1 << 20, 3), datagen.zipf_text(300000, 4), np.zeros(1 << 20, np.uint8)]
     comp, dec, status, sizes, actual = g.roundtrip("lz4", chunks, max_chunk=1 << 20)
     for i, c in enumerate(chunks):
+        # above 64 KiB the encoder keeps the reference's policy: same bytes as the reference-policy oracle
         assert comp[i].tobytes() == o.lz4_compress(c, 1, 1 << 20).tobytes()
         assert dec[i].tobytes() == c.tobytes() and status[i] == 0
     # NULL actual_bytes / statuses are allowed (reference SUPPORT_NULLPTR_APIS)

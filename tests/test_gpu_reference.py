@@ -49,8 +49,11 @@ def chunks_for(max_chunk, seed):
 
 
 @pytest.mark.parametrize("codec,max_chunk,type_id", [("lz4", 65536, 0), ("lz4", 4096, 0), ("lz4", 65536, 3), ("lz4", 65536, 4),
-                                                     ("snappy", 65536, 0), ("snappy", 4096, 0)])
-def test_lz_streams_identical_to_reference_gpu(libs, codec, max_chunk, type_id):
+                                                     ("lz4", 131072, 0), ("snappy", 65536, 0), ("snappy", 4096, 0)])
+def test_lz_streams_vs_reference_gpu(libs, codec, max_chunk, type_id):
+    """Our streams against the reference's own GPU build: each library decodes the other's output; our total
+    compressed size is within 1 % of (in practice below) the reference's; where we keep the reference's policy
+    (Snappy; LZ4 chunks above 64 KiB) the bytes are identical."""
     g, ours, ref = libs
     w = {0: 1, 3: 2, 4: 4}[type_id]
     chunks = [c[: len(c) // w * w] for c in chunks_for(max_chunk, 31 + max_chunk + type_id)]
@@ -58,9 +61,13 @@ def test_lz_streams_identical_to_reference_gpu(libs, codec, max_chunk, type_id):
     opts = g.L.LZ4Opts(type_id) if codec == "lz4" else None
     a = run_with(g, ours, lambda: g.roundtrip(codec, chunks, opts=opts, max_chunk=max_chunk))
     b = run_with(g, ref, lambda: g.roundtrip(codec, chunks, opts=opts, max_chunk=max_chunk))
+    identical = not (codec == "lz4" and max_chunk <= 65536)
     for i, c in enumerate(chunks):
-        assert a[0][i].tobytes() == b[0][i].tobytes(), f"chunk {i} (len {len(c)}): stream differs from the reference GPU encoder"
+        if identical:
+            assert a[0][i].tobytes() == b[0][i].tobytes(), f"chunk {i} (len {len(c)}): stream differs from the reference GPU encoder"
         assert b[1][i].tobytes() == c.tobytes() and a[1][i].tobytes() == c.tobytes()
+    ours_total, ref_total = sum(len(x) for x in a[0]), sum(len(x) for x in b[0])
+    assert ours_total <= 1.01 * ref_total, f"compressed {ours_total} B vs reference {ref_total} B"
     # cross decode: reference decoder on our streams, our decoder on the reference's
     caps = [len(c) for c in chunks]
     out, actual, status = run_with(g, ref, lambda: g.decode_raw(codec, a[0], caps))

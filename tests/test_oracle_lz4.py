@@ -100,3 +100,28 @@ def test_ratio_close_to_liblz4():
     ours = sum(len(o.lz4_compress(raw[i : i + 65536])) for i in range(0, len(raw), 65536))
     stock = sum(len(stock_compress(raw[i : i + 65536])) for i in range(0, len(raw), 65536))
     assert ours < 1.3 * stock
+
+
+@pytest.mark.parametrize("size", [1, 4, 5, 11, 12, 13, 14, 31, 32, 33, 64, 255, 1000, 1023, 1024, 1025, 2048, 4096, 5000,
+                                  16384, 40000, 65535, 65536])
+def test_team_model_streams_are_lz4_blocks(size):
+    """oracle/lz4_team_model.c (the sequential statement of the CUDA team encoder) emits plain LZ4 blocks:
+    liblz4 and the reference-policy oracle decoder decode them, and they fit GetMaxOutputChunkSize."""
+    for chunk in datagen.mixed_chunks(size, 6, 300 + size):
+        comp = o.lz4_team_compress(chunk, size)
+        assert 0 < len(comp) <= o.lz4_max_compressed(size)
+        n, out = stock_decompress(comp, size)
+        assert n == size and out.tobytes() == chunk.tobytes()
+        st, out = o.lz4_decompress(comp, size)
+        assert st == o.SUCCESS and out.tobytes() == chunk.tobytes()
+
+
+def test_team_model_ratio_not_below_reference_policy():
+    for gen, seed in ((datagen.log_lines, 5), (datagen.zipf_text, 6)):
+        raw = gen(1 << 20, seed)
+        chunks = [raw[i : i + 65536] for i in range(0, len(raw), 65536)]
+        team = sum(len(o.lz4_team_compress(c, 65536)) for c in chunks)
+        ref = sum(len(o.lz4_compress(c, 1, 65536)) for c in chunks)
+        assert team <= ref * 1.01
+    z = np.zeros(65536, np.uint8)
+    assert len(o.lz4_team_compress(z, 65536)) == len(o.lz4_compress(z, 1, 65536))  # runs merge across segments
