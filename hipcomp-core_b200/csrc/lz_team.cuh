@@ -32,17 +32,21 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
 // blocks (hardware sleep inside try_wait) until the phase with the given parity has completed
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
 {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "B200_MBAR_WAIT:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n"
-      "@p bra B200_MBAR_DONE;\n"
-      "bra B200_MBAR_WAIT;\n"
-      "B200_MBAR_DONE:\n"
-      "}\n" ::"r"(smem_addr(bar)),
-      "r"(parity)
-      : "memory");
+  const uint32_t a = smem_addr(bar);
+  for (;;) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(a), "r"(parity)
+        : "memory");
+    if (done) return;
+    __nanosleep(40); // leave the issue slots to the warps that have work
+  }
 }
 // generic-proxy accesses to shared memory made so far are ordered before later async-proxy ones
 __device__ __forceinline__ void fence_proxy_async()
@@ -78,6 +82,10 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t sa)
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(sa));
   return v;
+}
+__device__ __forceinline__ void sts_u16(uint32_t sa, uint32_t v)
+{
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(sa), "h"((unsigned short)v) : "memory");
 }
 // 4 bytes at any shared address: two aligned words + funnel shift
 __device__ __forceinline__ uint32_t lds_u32_unaligned(uint32_t sa)

@@ -8,11 +8,12 @@
  * and ratio parity against lz4_oracle_compress.
  *
  * Policy (every number below is mirrored in lz4_team.cuh):
- *   - all positions p <= n - 12 are hashed, h = (le32(p) * 2654435761) >> (32 - hash_log), in
- *     aligned windows of 32 positions.  A position whose hash already occurs at a lower position
- *     of its window takes the nearest such position as its candidate; every other position takes
- *     the table entry of its hash and replaces it (the table therefore keeps, per hash, the first
- *     position of the most recent window that contained it).  d[p] = p - candidate (0 = none).
+ *   - all positions p <= n - 12 get a candidate distance d[p] (0 = none).  A position whose 4 bytes
+ *     equal the 4 bytes 4 (else 8, else 1) positions earlier takes that distance (runs and repeated 1/2/4/8-byte
+ *     elements never touch the table).  Every other position is hashed,
+ *     h = (le32(p) * 2654435761) >> (32 - hash_log), and takes the table entry of its hash as the
+ *     table stood before its aligned window of 32 positions; after the window the table holds, per
+ *     hash, the highest such position of the window.
  *   - the chunk is cut into segments of 1024 positions.  Inside a segment the parse is
  *     greedy over 32-position windows that start at the cursor: the first position of the
  *     window whose candidate's 4 bytes match starts a match, extended up to
@@ -65,20 +66,24 @@ size_t lz4_team_model_compress(const uint8_t* in, size_t n_, uint8_t* out, int h
   const uint32_t npos = n >= 12 ? n - 11 : 0;
   const uint32_t mlimit = n >= 5 ? n - 5 : 0;
   for (uint32_t w0 = 0; w0 < npos; w0 += 32) {
-    uint32_t h[32];
+    uint32_t h[32], told[32];
     const uint32_t cnt = npos - w0 < 32 ? npos - w0 : 32;
-    for (uint32_t l = 0; l < cnt; ++l) h[l] = (ld32(in + w0 + l) * 2654435761u) >> (32 - hash_log);
+    for (uint32_t l = 0; l < cnt; ++l) {
+      const uint32_t p = w0 + l, key = ld32(in + p);
+      if (p >= 4 && key == ld32(in + p - 4)) h[l] = 0x8004u;      /* settled without the table */
+      else if (p >= 8 && key == ld32(in + p - 8)) h[l] = 0x8008u;
+      else if (p >= 1 && key == ld32(in + p - 1)) h[l] = 0x8001u;
+      else h[l] = (key * 2654435761u) >> (32 - hash_log);
+    }
+    /* the window reads the table as the previous windows left it ... */
+    for (uint32_t l = 0; l < cnt; ++l) told[l] = (h[l] & 0x8000u) ? 0 : table[h[l]];
     for (uint32_t l = 0; l < cnt; ++l) {
       const uint32_t p = w0 + l;
-      int twin = -1;
-      for (int u = (int)l - 1; u >= 0; --u)
-        if (h[u] == h[l]) { twin = u; break; }
-      if (twin >= 0) {
-        d[p] = (uint16_t)(l - (uint32_t)twin); /* nearest lower position of the window with the same hash */
+      if (h[l] & 0x8000u) {
+        d[p] = (uint16_t)(h[l] & 0x7fffu);
       } else {
-        const uint32_t t = table[h[l]];      /* first position of an earlier window with this hash ... */
-        d[p] = t < p ? (uint16_t)(p - t) : 0;
-        table[h[l]] = (uint16_t)p;           /* ... and the first one of this window replaces it */
+        d[p] = told[l] < p ? (uint16_t)(p - told[l]) : 0;
+        table[h[l]] = (uint16_t)p; /* ... and leaves its highest position per hash */
       }
     }
   }
