@@ -1,27 +1,86 @@
 #!/usr/bin/env python
-"""Per-source-line instruction counts / stall samples from an ncu report (cuda,sass view).
-usage: ncu_lines.py report.ncu-rep kernel_regex [top_n]"""
-import csv, subprocess, sys
-rep, kern = sys.argv[1], sys.argv[2]
-top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", "--kernel-name",
-                      "regex:" + kern], capture_output=True, text=True).stdout
-fname, hdr, recs, on = None, None, [], True
-for r in csv.reader(out.splitlines()):
-    if len(r) >= 2 and r[0] == "File Path":
-        fname = r[1].split("/")[-1]; hdr = None; continue
-    if len(r) >= 2 and r[0] == "Function Name":
-        on = kern.split("|")[0].replace("\\", "") in r[1] or True; continue
-    if len(r) > 3 and r[0] == "Line No":
-        hdr = r; ii = hdr.index("Instructions Executed"); si = hdr.index("# Samples"); continue
-    if hdr and len(r) > max(ii, si) and r[0] and r[0].isdigit():
-        try:
-            ie = int(r[ii]); ss = int(r[si])
-        except ValueError:
+"""Per-source-line instruction counts and stall samples of one kernel in an ncu report.
+
+ncu's csv source page is per SASS instruction and carries no line numbers, so the SASS rows are joined, in order,
+with `nvdisasm -g` of the same kernel taken from the library the report was made with (build with -lineinfo).
+
+  ncu_lines.py report.ncu-rep <kernel-regex> [lib.so] [top N]
+"""
+import csv
+import io
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+rep, pat = sys.argv[1], sys.argv[2]
+lib = sys.argv[3] if len(sys.argv) > 3 else os.path.join(os.path.dirname(__file__), "..", "hipcomp-core_b200", "lib", "libhipcomp.so")
+top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", f"regex:{pat}"],
+                     capture_output=True, text=True).stdout
+blocks = out.split('"Kernel Name",')
+blk = blocks[1]
+kname = blk.splitlines()[0]
+rows = list(csv.reader(io.StringIO("\n".join(blk.splitlines()[1:]))))
+h = rows[0]
+iS, iI, iN = h.index("Source"), h.index("Instructions Executed"), h.index("# Samples")
+stall_cols = [(i, n) for i, n in enumerate(h) if n.startswith("stall_") and "Not Issued" not in n]
+sass = [r for r in rows[1:] if len(r) == len(h)]
+
+tmp = tempfile.mkdtemp()
+subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, capture_output=True)
+func = re.search(r"void (?:\w+::)*(\w+)", kname).group(1)
+lines = None
+for f in os.listdir(tmp):
+    dis = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
+    # split by .text sections; pick the one whose demangled template args match
+    secs = re.split(r"^\s*\.text\.", dis, flags=re.M)
+    for s in secs[1:]:
+        name = s.split(":", 1)[0]
+        if func not in name:
             continue
-        if ie or ss:
-            recs.append((ie, ss, fname, r[0], r[1].strip()[:110]))
-ti = sum(r[0] for r in recs); ts = sum(r[1] for r in recs)
-print(f"total inst {ti}  samples {ts}")
-for ie, ss, f, ln, src in sorted(recs, key=lambda r: -r[0])[:top]:
-    print(f"{100*ie/max(ti,1):5.1f}%i {100*ss/max(ts,1):5.1f}%s {f}:{ln:>4} {src}")
+        cur, seq, fresh = None, [], True
+        for ln in s.splitlines():
+            m = re.search(r'//## File "([^"]+)", line (\d+)(?: inlined at "([^"]+)", line (\d+))?', ln)
+            if m:
+                # -gi prints the inline chain innermost first; keep the outermost frame (the kernel's own line)
+                if m.group(3):
+                    cur = (os.path.basename(m.group(3)), int(m.group(4)))
+                else:
+                    cur = (os.path.basename(m.group(1)), int(m.group(2)))
+                continue
+            if re.match(r"\s+/\*[0-9a-f]{4}\*/", ln):
+                seq.append(cur)
+        if len(seq) == len(sass):
+            lines = seq
+            break
+    if lines:
+        break
+if lines is None:
+    sys.exit(f"no disassembled function named {func} with {len(sass)} instructions")
+
+agg = {}
+tot_i = tot_s = 0
+for r, loc in zip(sass, lines):
+    a = agg.setdefault(loc, [0, 0, {}])
+    a[0] += int(r[iI])
+    a[1] += int(r[iN])
+    tot_i += int(r[iI])
+    tot_s += int(r[iN])
+    for i, n in stall_cols:
+        v = int(r[i] or 0)
+        if v:
+            a[2][n] = a[2].get(n, 0) + v
+print(f"{kname[:100]}\ninstructions {tot_i}, samples {tot_s}")
+src_cache = {}
+for loc, (ni, ns, st) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+    txt = ""
+    if loc:
+        p = os.path.join(os.path.dirname(__file__), "..", "hipcomp-core_b200", "csrc", loc[0])
+        if os.path.exists(p):
+            src_cache.setdefault(p, open(p).read().splitlines())
+            txt = src_cache[p][loc[1] - 1].strip()[:90]
+    tops = ", ".join(f"{k[6:]} {v}" for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:3])
+    print(f"{100 * ni / tot_i:5.1f}% inst {100 * ns / max(tot_s, 1):5.1f}% smpl  {loc}  {txt}   [{tops}]")
