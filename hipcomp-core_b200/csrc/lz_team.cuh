@@ -29,7 +29,8 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
 {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
 }
-// blocks (hardware sleep inside try_wait) until the phase with the given parity has completed
+// blocks until the phase with the given parity has completed (try_wait suspends in hardware for a while; the
+// short sleep between attempts keeps a waiting warp from eating the issue slots of the working ones)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
 {
   const uint32_t a = smem_addr(bar);
@@ -38,14 +39,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x989680;\n"
         "selp.u32 %0, 1, 0, p;\n"
         "}\n"
         : "=r"(done)
         : "r"(a), "r"(parity)
         : "memory");
     if (done) return;
-    __nanosleep(40); // leave the issue slots to the warps that have work
+    __nanosleep(64);
   }
 }
 // generic-proxy accesses to shared memory made so far are ordered before later async-proxy ones
@@ -86,6 +87,17 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t sa)
 __device__ __forceinline__ void sts_u16(uint32_t sa, uint32_t v)
 {
   asm volatile("st.shared.u16 [%0], %1;" ::"r"(sa), "h"((unsigned short)v) : "memory");
+}
+// table accesses of the encoders' serial section (explicit shared-space instructions, kept in program order)
+__device__ __forceinline__ uint32_t lds_u32_ordered(uint32_t sa)
+{
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(sa) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_max_u32(uint32_t sa, uint32_t v)
+{
+  asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(sa), "r"(v) : "memory");
 }
 // 4 bytes at any shared address: two aligned words + funnel shift
 __device__ __forceinline__ uint32_t lds_u32_unaligned(uint32_t sa)
