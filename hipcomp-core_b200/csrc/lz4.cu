@@ -11,7 +11,7 @@
 // the caller's workspace, last-lane-wins insertion) byte for byte.
 // The decoder bounds every compressed read (the reference's does not).
 #include "lz_common.cuh"
-#include "lz4_team.cuh"
+#include "lz_team_encode.cuh"
 #include "lz_pipeline.cuh"
 
 #include <cstdlib>
@@ -724,19 +724,59 @@ __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_byt
   }
 }
 
-// ---- team encoder launch (lz4_team.cuh).  Hash-table bits and team width by declared chunk size;
-//      oracle/lz4_team_model.c is called with the same hash_log by the tests.
+// ---- team encoder (lz_team_encode.cuh): how an LZ4 sequence is sized and written.  Hash-table bits and team
+//      width by declared chunk size; oracle/lz_team_model.c is called with the same hash_log by the tests.
 constexpr size_t kTeamMaxChunk = 65536;
+
+struct TeamEmit {
+  static constexpr bool kNeedDist = false;
+  static __device__ __forceinline__ uint32_t lsic_bytes(uint32_t x) { return x >= 15u ? (x - 15u) / 255u + 1u : 0u; }
+  static __device__ __forceinline__ uint32_t empty_stream(uint8_t*) { return 0; }
+  static __device__ __forceinline__ uint32_t preamble(uint8_t*, uint32_t, uint32_t) { return 0; }
+  static __device__ __forceinline__ uint32_t lit_bytes(uint32_t nlit) { return nlit + lsic_bytes(nlit); }
+  // token + offset + match length bytes
+  static __device__ __forceinline__ uint32_t match_bytes(uint32_t len, uint32_t) { return 3u + lsic_bytes(len - 4u); }
+  static __device__ __forceinline__ uint8_t* put_lit_header(uint8_t* o, uint32_t nlit, uint32_t len)
+  {
+    const uint32_t ml = len - 4u;
+    *o++ = (uint8_t)(((nlit >= 15u ? 15u : nlit) << 4) | (ml >= 15u ? 15u : ml));
+    if (nlit >= 15u) {
+      uint32_t x = nlit - 15u;
+      for (; x >= 255u; x -= 255u) *o++ = 0xff;
+      *o++ = (uint8_t)x;
+    }
+    return o;
+  }
+  static __device__ __forceinline__ uint8_t* put_match(uint8_t* o, uint32_t d, uint32_t len)
+  {
+    o[0] = (uint8_t)(d & 0xffu);
+    o[1] = (uint8_t)(d >> 8);
+    o += 2;
+    const uint32_t ml = len - 4u;
+    if (ml >= 15u) {
+      uint32_t x = ml - 15u;
+      for (; x >= 255u; x -= 255u) *o++ = 0xff;
+      *o++ = (uint8_t)x;
+    }
+    return o;
+  }
+  // header of the final literals, written by the whole warp; returns its size
+  static __device__ __forceinline__ uint32_t put_tail_header(uint8_t* o, uint32_t nlit, uint32_t lane)
+  {
+    if (lane == 0) o[0] = (uint8_t)((nlit >= 15u ? 15u : nlit) << 4);
+    return 1u + (nlit >= 15u ? team::put_lsic(o + 1, nlit - 15u) : 0u);
+  }
+};
 
 template <int CAP, int HL, int W>
 static void launch_team_cfg(const void* const* in_ptrs, const size_t* in_bytes, size_t batch, void* const* out_ptrs,
                             size_t* out_bytes, cudaStream_t stream, int ctas_per_sm)
 {
-  using L = TeamLayout<CAP, HL, W>;
-  allow_smem(compress_team_kernel<CAP, HL, W>, (int)L::kBytes);
+  using L = team::TeamLayout<CAP, HL, W>;
+  allow_smem(team::compress_team_kernel<TeamEmit, CAP, HL, W>, (int)L::kBytes);
   const size_t cap = (size_t)sm_count() * ctas_per_sm;
   const int grid = (int)(batch < cap ? batch : cap);
-  compress_team_kernel<CAP, HL, W><<<grid, W * 32, L::kBytes, stream>>>(in_ptrs, in_bytes, out_ptrs, out_bytes, batch);
+  team::compress_team_kernel<TeamEmit, CAP, HL, W><<<grid, W * 32, L::kBytes, stream>>>(in_ptrs, in_bytes, out_ptrs, out_bytes, batch);
 }
 
 static void launch_team(const void* const* in_ptrs, const size_t* in_bytes, size_t max_chunk, size_t batch,

@@ -4,7 +4,7 @@
 // launched by src/lowlevel/LZ4CompressionKernels.hip:73-94), whose per-window chain
 // "key -> table probe -> verify -> extend" is serial per chunk.  The output is a plain LZ4 block
 // (decodable by the reference decoder and by liblz4) but not the reference's byte stream; the
-// policy is stated sequentially in oracle/lz4_team_model.c, which the tests compare against byte
+// policy is stated sequentially in oracle/lz_team_model.c, which the tests compare against byte
 // for byte.
 //
 // Data movement: the chunk is staged in shared memory by one bulk copy (cp.async.bulk +
@@ -29,9 +29,8 @@
 #include "lz_team.cuh"
 
 namespace b200comp {
-namespace lz4 {
+namespace team {
 
-using team::kSeg;
 constexpr uint32_t kLaneSteps = 15; // further 4-byte words a lane verifies behind the first 4 bytes of its match
 
 template <int CAP, int HL, int W>
@@ -46,7 +45,7 @@ struct TeamLayout {
   static constexpr uint32_t kBytes = kDummyOff + 128 * W;     // a word per lane for the lanes without a table slot
 };
 
-template <int CAP, int HL, int W>
+template <class Emit, int CAP, int HL, int W>
 __global__ void __launch_bounds__(W * 32, (CAP > 16384 ? 1 : (CAP > 4096 ? 3 : 6)))
 compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
                      size_t batch)
@@ -70,13 +69,13 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
   const unsigned lt_mask = lanemask_lt();
 
   if (threadIdx.x == 0) {
-    team::mbar_init(load_bar, 1);
+    mbar_init(load_bar, 1);
     for (int w = 0; w < W; ++w) {
-      team::mbar_init(turn_bar + 2 * w, 1);
-      team::mbar_init(pub_bar + 2 * w, 1);
-      team::mbar_init(x_bar + 2 * w, 1);
+      mbar_init(turn_bar + 2 * w, 1);
+      mbar_init(pub_bar + 2 * w, 1);
+      mbar_init(x_bar + 2 * w, 1);
     }
-    team::mbar_init_fence();
+    mbar_init_fence();
   }
   uint32_t load_phase = 0, turn_phase = 0, pub_phase = 0, x_phase = 0;
 
@@ -85,18 +84,18 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
     const uint8_t* src = static_cast<const uint8_t*>(in_ptrs[chunk]);
     uint8_t* gout = static_cast<uint8_t*>(out_ptrs[chunk]);
     const size_t n64 = in_bytes[chunk];
-    if (n64 == 0 || n64 > (size_t)CAP) { // empty chunk -> empty stream; larger than the caller's declared maximum -> 0
-      if (threadIdx.x == 0) out_bytes[chunk] = 0;
+    if (n64 == 0 || n64 > (size_t)CAP) { // empty chunk -> the codec's empty stream; larger than the caller's declared maximum -> 0
+      if (threadIdx.x == 0) out_bytes[chunk] = n64 == 0 ? Emit::empty_stream(gout) : 0;
       continue;
     }
     const uint32_t n = (uint32_t)n64;
-    const uint32_t mis = team::stage_chunk(s_chunk, src, n, load_bar);
+    const uint32_t mis = stage_chunk(s_chunk, src, n, load_bar);
     {
       uint4* t128 = reinterpret_cast<uint4*>(s_table);
       const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
       for (uint32_t i = threadIdx.x; i < (4u << HL) / 16u; i += W * 32) t128[i] = zero;
     }
-    team::mbar_wait(load_bar, load_phase);
+    mbar_wait(load_bar, load_phase);
     load_phase ^= 1u;
     __syncthreads();
 
@@ -106,9 +105,9 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
     uint16_t* db = s_dbuf + warp * kSeg;
     uint16_t* ends = s_ends + warp * 256u;          // [k * 32 + lane]
     const uint32_t nextw = (warp + 1u) % W;
-    const uint32_t chunk_sa = team::smem_addr(s_chunk) + mis; // shared address of chunk byte 0
-    const uint32_t db_sa = team::smem_addr(db);
-    const uint32_t ends_sa = team::smem_addr(ends) + 2u * lane;
+    const uint32_t chunk_sa = smem_addr(s_chunk) + mis; // shared address of chunk byte 0
+    const uint32_t db_sa = smem_addr(db);
+    const uint32_t ends_sa = smem_addr(ends) + 2u * lane;
 
     for (uint32_t s = warp; s < nseg; s += W) {
       const uint32_t S0 = s * kSeg;
@@ -150,8 +149,8 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
       //         table holds the highest position per hash whatever the order inside the window.
       uint32_t cand = 0; // positions of the lane's block whose candidate holds
       {
-        const uint32_t table_sa = team::smem_addr(s_table);
-        const uint32_t dummy_sa = team::smem_addr(smem + L::kDummyOff) + 128u * warp + 4u * lane;
+        const uint32_t table_sa = smem_addr(s_table);
+        const uint32_t dummy_sa = smem_addr(smem + L::kDummyOff) + 128u * warp + 4u * lane;
         uint32_t sa[32]; // shared address of the lane's table slot per window (or its dummy word); then the slot's old value
 #pragma unroll
         for (int u = 0; u < 32; ++u) {
@@ -160,7 +159,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
           sa[u] = (rec & 0x8000u) ? dummy_sa : table_sa + 4u * rec;
         }
         if (s > 0) {
-          team::mbar_wait(turn_bar + 2 * warp, turn_phase);
+          mbar_wait(turn_bar + 2 * warp, turn_phase);
           turn_phase ^= 1u;
         }
         __syncwarp();
@@ -171,12 +170,12 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
 #pragma unroll
         for (int u = 0; u < 32; ++u) {
           const uint32_t a = sa[u];
-          sa[u] = team::lds_u32_ordered(a);
-          team::red_max_u32(a, pp1 + 32u * u);
+          sa[u] = lds_u32_ordered(a);
+          red_max_u32(a, pp1 + 32u * u);
           if ((u & 7) == 7) __syncwarp();
         }
         if (s + 1 < nseg) {
-          if (lane == 0) team::mbar_arrive(turn_bar + 2 * nextw);
+          if (lane == 0) mbar_arrive(turn_bar + 2 * nextw);
         }
         // distances, and which candidates hold: the 4 bytes at p and at p - d[p] are equal.  Window u is the
         // block of lane u, which keeps the window's ballot as its candidate bitmap.
@@ -190,7 +189,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
             const uint32_t d = (rec & 0x8000u) ? (rec & 0x7FFFu) : (t ? pp1 + 32u * u - t : 0u);
             db[i] = (uint16_t)d;
             const uint32_t pa = chunk_sa + S0 + i;
-            if (d) ok = team::lds_u32_unaligned(pa) == team::lds_u32_unaligned(pa - d);
+            if (d) ok = lds_u32_unaligned(pa) == lds_u32_unaligned(pa - d);
           }
           const unsigned wm = __ballot_sync(kFull, ok);
           if ((int)lane == u) cand = wm;
@@ -213,10 +212,10 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
           if (!ext) {
             const uint32_t bit = (uint32_t)__ffs((int)cand) - 1u;
             q = B0 + bit;
-            d = team::lds_u16(db_sa + 2u * (q - S0));
+            d = lds_u16(db_sa + 2u * (q - S0));
             m = q + 4u, steps = 0, ext = true; // m < E: q <= n - 12
           }
-          const uint32_t x = team::lds_u32_unaligned(chunk_sa + m) ^ team::lds_u32_unaligned(chunk_sa + m - d);
+          const uint32_t x = lds_u32_unaligned(chunk_sa + m) ^ lds_u32_unaligned(chunk_sa + m - d);
           bool done = true;
           uint32_t end;
           if (x) {
@@ -235,7 +234,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
           }
           if (done) {
             bm |= 1u << (q - B0);
-            team::sts_u16(ends_sa + 64u * nm, end);
+            sts_u16(ends_sa + 64u * nm, end);
             ++nm;
             v = end;
             ext = false;
@@ -251,7 +250,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
       //          warp compares 128 bytes per step up to the true end.
       uint32_t Xin = 0;
       if (s > 0) {
-        team::mbar_wait(x_bar + 2 * warp, x_phase);
+        mbar_wait(x_bar + 2 * warp, x_phase);
         x_phase ^= 1u;
         Xin = s_xstate[warp].x;
       }
@@ -270,7 +269,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
             for (uint32_t a0 = vl; a0 < E; a0 += 128u) {
               const uint32_t a = a0 + 4u * lane;
               uint32_t x = 1u;
-              if (a < E) x = team::lds_u32_unaligned(chunk_sa + a) ^ team::lds_u32_unaligned(chunk_sa + a - dq);
+              if (a < E) x = lds_u32_unaligned(chunk_sa + a) ^ lds_u32_unaligned(chunk_sa + a - dq);
               const unsigned diff = __ballot_sync(kFull, x != 0u);
               if (diff) {
                 const int fl = __ffs((int)diff) - 1;
@@ -281,7 +280,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
             }
             if ((int)lane == ll) {
               v = mq;
-              team::sts_u16(ends_sa + 64u * (nm - 1u), mq);
+              sts_u16(ends_sa + 64u * (nm - 1u), mq);
             }
           }
         }
@@ -290,7 +289,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
         const uint32_t Xout = max(Xin, __reduce_max_sync(kFull, v));
         if (lane == 0) {
           s_xstate[nextw] = make_uint4(Xout, 0u, 0u, 0u);
-          team::mbar_arrive(x_bar + 2 * nextw);
+          mbar_arrive(x_bar + 2 * nextw);
         }
       }
       // X in front of every lane: exclusive prefix maximum of the lanes' last match ends
@@ -310,25 +309,24 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
       //          are the first ones of the lane), the first survivor starts at max(start, X), the others are
       //          unchanged.  Sizes of everything but the segment's first literal run (it starts at the
       //          predecessor's last emitted match end, which arrives with the output cursor).
-      auto lsic_bytes = [](uint32_t x) -> uint32_t { return x >= 15u ? (x - 15u) / 255u + 1u : 0u; };
       uint32_t em = 0, kfirst = 0, sfirst = 0, bytes = 0, last_end = 0;
       {
         uint32_t b = bm, k = 0;
         bool found = false;
         while (b) {
           const uint32_t bit = (uint32_t)__ffs((int)b) - 1u;
-          const uint32_t q = B0 + bit, e = team::lds_u16(ends_sa + 64u * k);
+          const uint32_t q = B0 + bit, e = lds_u16(ends_sa + 64u * k);
           if (!found) {
             const uint32_t s0 = max(q, X);
             if (e >= s0 + 4u) {
               found = true;
               sfirst = s0, kfirst = k, em = b;
-              bytes = 3u + lsic_bytes(e - s0 - 4u);
+              bytes = Emit::match_bytes(e - s0, Emit::kNeedDist ? (uint32_t)db[32u * lane + bit] : 0u);
               last_end = e;
             }
           } else {
             const uint32_t nlit = q - last_end;
-            bytes += 3u + nlit + (nlit >= 15u ? 1u : 0u) + lsic_bytes(e - q - 4u); // nlit <= 27: at most one length byte
+            bytes += Emit::lit_bytes(nlit) + Emit::match_bytes(e - q, Emit::kNeedDist ? (uint32_t)db[32u * lane + bit] : 0u);
             last_end = e;
           }
           b &= b - 1u;
@@ -340,8 +338,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
       uint32_t Lf = __shfl_sync(kFull, last_end, lower ? 31 - __clz((int)lower) : 0); // where the lane's first literals begin
       const bool seg_first = em != 0u && lower == 0u;
       if (em != 0u && lower != 0u) {
-        const uint32_t nlit = sfirst - Lf;
-        bytes += nlit + lsic_bytes(nlit);
+        bytes += Emit::lit_bytes(sfirst - Lf);
       }
       uint32_t total;
       uint32_t lane_off = warp_excl_sum(bytes, total);
@@ -350,16 +347,16 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
 
       // ---- 4c. output chain: (output cursor, first literal not yet written)
       uint32_t ob = 0, Lin = 0;
+      if (s == 0) ob = Emit::preamble(gout, n, lane);
       if (s > 0) {
-        team::mbar_wait(pub_bar + 2 * warp, pub_phase);
+        mbar_wait(pub_bar + 2 * warp, pub_phase);
         pub_phase ^= 1u;
         const uint4 st = s_state[warp];
         ob = st.x, Lin = st.y;
       }
       uint32_t Lout = Lin;
       if (emit_mask) {
-        const uint32_t nlit = seg_sfirst - Lin;
-        const uint32_t extra = nlit + lsic_bytes(nlit);
+        const uint32_t extra = Emit::lit_bytes(seg_sfirst - Lin);
         total += extra;
         Lout = seg_last_end;
         if (seg_first) Lf = Lin;
@@ -368,7 +365,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
       if (s + 1 < nseg) {
         if (lane == 0) {
           s_state[nextw] = make_uint4(ob + total, Lout, 0u, 0u);
-          team::mbar_arrive(pub_bar + 2 * nextw);
+          mbar_arrive(pub_bar + 2 * nextw);
         }
       }
 
@@ -383,30 +380,18 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
           const uint32_t bit = (uint32_t)__ffs((int)b) - 1u;
           b &= b - 1u;
           const uint32_t q = first ? sfirst : B0 + bit;
-          const uint32_t e = team::lds_u16(ends_sa + 64u * k), dd = db[32u * lane + bit];
+          const uint32_t e = lds_u16(ends_sa + 64u * k), dd = db[32u * lane + bit];
           ++k;
           first = false;
-          const uint32_t nlit = q - pe, ml = e - q - 4u;
-          *o++ = (uint8_t)(((nlit >= 15u ? 15u : nlit) << 4) | (ml >= 15u ? 15u : ml));
-          if (nlit >= 15u) {
-            uint32_t x = nlit - 15u;
-            for (; x >= 255u; x -= 255u) *o++ = 0xff;
-            *o++ = (uint8_t)x;
-          }
+          const uint32_t nlit = q - pe;
+          o = Emit::put_lit_header(o, nlit, e - q);
           if (nlit <= 28u) {
             for (uint32_t i = 0; i < nlit; ++i) o[i] = s_chunk[mis + pe + i];
           } else { // at most one per lane: later sequences of the lane have fewer than 28 literals
             long_src = pe, long_cnt = nlit, long_dst = o;
           }
           o += nlit;
-          o[0] = (uint8_t)(dd & 0xffu);
-          o[1] = (uint8_t)(dd >> 8);
-          o += 2;
-          if (ml >= 15u) {
-            uint32_t x = ml - 15u;
-            for (; x >= 255u; x -= 255u) *o++ = 0xff;
-            *o++ = (uint8_t)x;
-          }
+          o = Emit::put_match(o, dd, e - q);
           pe = e;
         }
         // long literal runs: the whole warp copies them, one run at a time
@@ -416,17 +401,15 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
           longm &= longm - 1u;
           const uint32_t srcp = __shfl_sync(kFull, long_src, l), cntl = __shfl_sync(kFull, long_cnt, l);
           uint8_t* dst = reinterpret_cast<uint8_t*>(__shfl_sync(kFull, reinterpret_cast<unsigned long long>(long_dst), l));
-          team::copy_s2g(dst, s_chunk32, mis + srcp, cntl);
+          copy_s2g(dst, s_chunk32, mis + srcp, cntl);
         }
       }
       if (s + 1 == nseg) {
-        // last segment: the final sequence is literals only
+        // last segment: the final literals
         uint32_t o2 = ob + total;
         const uint32_t nlit = n - Lout;
-        if (lane == 0) gout[o2] = (uint8_t)((nlit >= 15u ? 15u : nlit) << 4);
-        o2 += 1u;
-        if (nlit >= 15u) o2 += team::put_lsic(gout + o2, nlit - 15u);
-        team::copy_s2g(gout + o2, s_chunk32, mis + Lout, nlit);
+        o2 += Emit::put_tail_header(gout + o2, nlit, lane);
+        copy_s2g(gout + o2, s_chunk32, mis + Lout, nlit);
         o2 += nlit;
         if (lane == 0) out_bytes[chunk] = o2;
       }
@@ -435,5 +418,5 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
   }
 }
 
-} // namespace lz4
+} // namespace team
 } // namespace b200comp

@@ -10,6 +10,7 @@
 // uses a 3-warp prefetch/decode/process pipeline with nanosleep spin queues).
 #include "lz_common.cuh"
 #include "lz_pipeline.cuh"
+#include "lz_team_encode.cuh"
 
 #include <cstdlib>
 
@@ -701,6 +702,106 @@ __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_byt
   }
 }
 
+// ---- team encoder (lz_team_encode.cuh) for chunks <= 64 KiB: how a Snappy sequence is sized and written
+//      (elements: src/snappy/symbol.hiph:43-70).  oracle/lz_team_model.c states the same sequentially.
+constexpr size_t kTeamMaxChunk = 65536;
+
+struct TeamEmit {
+  static constexpr bool kNeedDist = true;
+  static __device__ __forceinline__ uint32_t empty_stream(uint8_t* gout)
+  {
+    gout[0] = 0; // varint(0)
+    return 1;
+  }
+  // preamble: the uncompressed length as a varint
+  static __device__ __forceinline__ uint32_t preamble(uint8_t* gout, uint32_t n, uint32_t lane)
+  {
+    const uint32_t nb = n < 0x80u ? 1u : (n < 0x4000u ? 2u : 3u);
+    if (lane < nb) gout[lane] = (uint8_t)(((n >> (7u * lane)) & 0x7fu) | (lane + 1u < nb ? 0x80u : 0u));
+    return nb;
+  }
+  static __device__ __forceinline__ uint32_t lit_bytes(uint32_t nlit)
+  {
+    return nlit ? nlit + 1u + (nlit > 60u ? 1u : 0u) + (nlit > 256u ? 1u : 0u) : 0u;
+  }
+  // copies of 64 while 68 or more remain, one of 60 when more than 64 remain, then the rest (>= 4)
+  static __device__ __forceinline__ uint32_t match_bytes(uint32_t len, uint32_t d)
+  {
+    uint32_t bytes = 0;
+    if (len >= 68u) {
+      const uint32_t k = (len - 68u) / 64u + 1u;
+      bytes = 3u * k;
+      len -= 64u * k;
+    }
+    if (len > 64u) {
+      bytes += 3u;
+      len -= 60u;
+    }
+    return bytes + ((len < 12u && d < 2048u) ? 2u : 3u);
+  }
+  static __device__ __forceinline__ uint8_t* put_lit_header(uint8_t* o, uint32_t nlit, uint32_t)
+  {
+    if (nlit == 0u) return o;
+    const uint32_t l1 = nlit - 1u;
+    if (l1 < 60u) {
+      *o++ = (uint8_t)(l1 << 2);
+    } else if (l1 <= 0xffu) {
+      *o++ = (uint8_t)(60u << 2);
+      *o++ = (uint8_t)l1;
+    } else {
+      *o++ = (uint8_t)(61u << 2);
+      *o++ = (uint8_t)l1;
+      *o++ = (uint8_t)(l1 >> 8);
+    }
+    return o;
+  }
+  static __device__ __forceinline__ uint8_t* put_match(uint8_t* o, uint32_t d, uint32_t len)
+  {
+    while (len) {
+      uint32_t piece = len;
+      if (len >= 68u) piece = 64u;
+      else if (len > 64u) piece = 60u;
+      if (piece < 12u && d < 2048u) {
+        *o++ = (uint8_t)(((d & 0x700u) >> 3) | ((piece - 4u) << 2) | 0x01u);
+        *o++ = (uint8_t)d;
+      } else {
+        *o++ = (uint8_t)(((piece - 1u) << 2) | 0x2u);
+        *o++ = (uint8_t)d;
+        *o++ = (uint8_t)(d >> 8);
+      }
+      len -= piece;
+    }
+    return o;
+  }
+  static __device__ __forceinline__ uint32_t put_tail_header(uint8_t* o, uint32_t nlit, uint32_t lane)
+  {
+    if (lane == 0) put_lit_header(o, nlit, 0);
+    return lit_bytes(nlit) - nlit;
+  }
+};
+
+template <int CAP, int HL, int W>
+static void launch_team_cfg(const void* const* in_ptrs, const size_t* in_bytes, size_t batch, void* const* out_ptrs,
+                            size_t* out_bytes, cudaStream_t stream, int ctas_per_sm)
+{
+  using L = team::TeamLayout<CAP, HL, W>;
+  allow_smem(team::compress_team_kernel<TeamEmit, CAP, HL, W>, (int)L::kBytes);
+  const size_t cap = (size_t)sm_count() * ctas_per_sm;
+  const int grid = (int)(batch < cap ? batch : cap);
+  team::compress_team_kernel<TeamEmit, CAP, HL, W><<<grid, W * 32, L::kBytes, stream>>>(in_ptrs, in_bytes, out_ptrs, out_bytes, batch);
+}
+
+static void launch_team(const void* const* in_ptrs, const size_t* in_bytes, size_t max_chunk, size_t batch,
+                        void* const* out_ptrs, size_t* out_bytes, cudaStream_t stream)
+{
+  if (max_chunk <= 4096)
+    launch_team_cfg<4096, 12, 4>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 6);
+  else if (max_chunk <= 16384)
+    launch_team_cfg<16384, 13, 8>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 3);
+  else
+    launch_team_cfg<65536, 14, 20>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 1);
+}
+
 } // namespace snappy
 } // namespace b200comp
 
@@ -806,7 +907,8 @@ hipcompStatus_t hipcompBatchedSnappyCompressGetMaxOutputChunkSize(size_t max_chu
 }
 
 hipcompStatus_t hipcompBatchedSnappyCompressAsync(const void* const* device_uncompressed_ptr,
-                                                  const size_t* device_uncompressed_bytes, size_t, size_t batch_size,
+                                                  const size_t* device_uncompressed_bytes,
+                                                  size_t max_uncompressed_chunk_bytes, size_t batch_size,
                                                   void*, size_t, void* const* device_compressed_ptr,
                                                   size_t* device_compressed_bytes, hipcompBatchedSnappyOpts_t,
                                                   hipStream_t stream)
@@ -817,6 +919,12 @@ hipcompStatus_t hipcompBatchedSnappyCompressAsync(const void* const* device_unco
   B200_CHECK_NOT_NULL(device_compressed_ptr, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   if (batch_size == 0) return hipcompSuccess;
+  if (max_uncompressed_chunk_bytes != 0 && max_uncompressed_chunk_bytes <= snappy::kTeamMaxChunk) {
+    snappy::launch_team(device_uncompressed_ptr, device_uncompressed_bytes, max_uncompressed_chunk_bytes, batch_size,
+                        device_compressed_ptr, device_compressed_bytes, stream);
+    return check_launch(fn);
+  }
+  // larger (or undeclared) chunk sizes: the reference-policy warp encoder
   const size_t sms = (size_t)sm_count();
   constexpr size_t kMapBytes = sizeof(uint16_t) << snappy::kHashBits;
   // waves over the batch: 24 warps per SM as 6 CTAs of 4, or 28 as one CTA

@@ -1,13 +1,14 @@
 /*
- * TEST INFRASTRUCTURE — CPU model of b200comp's own LZ4 encoder for chunks <= 64 KiB
- * (hipcomp-core_b200/csrc/lz4_team.cuh).  It is NOT a restatement of the reference: the
- * reference's greedy one-warp encoder (src/LZ4Kernels.hiph:793-969) is restated in
- * lz4_oracle.c.  This file states, sequentially, the policy the CUDA kernel implements in
+ * TEST INFRASTRUCTURE — CPU model of b200comp's own LZ4 and Snappy encoders for chunks <= 64 KiB
+ * (hipcomp-core_b200/csrc/lz_team_encode.cuh; the two codecs share the match finder and differ in how a
+ * sequence is written).  It is NOT a restatement of the reference: the
+ * reference's greedy encoders (src/LZ4Kernels.hiph:793-969, src/snappy/compression.hiph:190-385) are
+ * restated in lz4_oracle.c / snappy_oracle.c.  This file states, sequentially, the policy the CUDA kernel implements in
  * parallel, so that tests can demand byte-identical output from the GPU (any divergence is a
  * kernel bug) while format parity is checked separately with liblz4 / the reference decoder
  * and ratio parity against lz4_oracle_compress.
  *
- * Policy (every number below is mirrored in lz4_team.cuh):
+ * Policy (every number below is mirrored in lz_team_encode.cuh):
  *   1. candidates.  Every position p <= n - 12 gets a candidate distance d[p] (0 = none).  A position whose
  *      4 bytes equal the 4 bytes 4 (else 8, else 1) positions earlier takes that distance (runs and repeated
  *      1/2/4/8-byte elements never touch the table).  Every other position is hashed,
@@ -39,12 +40,71 @@ static size_t put_lsic(uint8_t* out, size_t pos, uint32_t x)
   return pos;
 }
 
-size_t lz4_team_model_compress(const uint8_t* in, size_t n_, uint8_t* out, int hash_log)
+/* a sequence: literals [L, s) followed by a match of length m - s at distance dq (m == s: the final literals) */
+typedef size_t (*emit_fn)(uint8_t* out, size_t c, const uint8_t* in, uint32_t L, uint32_t s, uint32_t m, uint32_t dq);
+
+static size_t lz4_emit(uint8_t* out, size_t c, const uint8_t* in, uint32_t L, uint32_t s, uint32_t m, uint32_t dq)
+{
+  const uint32_t nlit = s - L;
+  if (m == s) { /* last sequence: literals only */
+    out[c++] = (uint8_t)((nlit >= 15 ? 15 : nlit) << 4);
+    if (nlit >= 15) c = put_lsic(out, c, nlit - 15);
+    memcpy(out + c, in + L, nlit);
+    return c + nlit;
+  }
+  const uint32_t ml = m - s - 4;
+  out[c++] = (uint8_t)(((nlit >= 15 ? 15 : nlit) << 4) | (ml >= 15 ? 15 : ml));
+  if (nlit >= 15) c = put_lsic(out, c, nlit - 15);
+  memcpy(out + c, in + L, nlit);
+  c += nlit;
+  out[c++] = (uint8_t)(dq & 0xff);
+  out[c++] = (uint8_t)(dq >> 8);
+  if (ml >= 15) c = put_lsic(out, c, ml - 15);
+  return c;
+}
+
+/* Snappy elements (format: share/snappy/hipcomp_snappy.py:113-181, src/snappy/symbol.hiph:43-70): one literal
+ * element when there are literals, then copies of at most 64 bytes; the 2-byte copy form when it fits. */
+static size_t snappy_emit(uint8_t* out, size_t c, const uint8_t* in, uint32_t L, uint32_t s, uint32_t m, uint32_t dq)
+{
+  const uint32_t nlit = s - L;
+  if (nlit) {
+    const uint32_t l1 = nlit - 1;
+    if (l1 < 60) {
+      out[c++] = (uint8_t)(l1 << 2);
+    } else if (l1 <= 0xff) {
+      out[c++] = 60 << 2;
+      out[c++] = (uint8_t)l1;
+    } else {
+      out[c++] = 61 << 2;
+      out[c++] = (uint8_t)l1;
+      out[c++] = (uint8_t)(l1 >> 8);
+    }
+    memcpy(out + c, in + L, nlit);
+    c += nlit;
+  }
+  uint32_t len = m - s;
+  while (len) {
+    uint32_t piece = len;
+    if (len >= 68) piece = 64;
+    else if (len > 64) piece = 60; /* leaves at least 4 for the last copy */
+    if (piece < 12 && dq < 2048) {
+      out[c++] = (uint8_t)(((dq & 0x700) >> 3) | ((piece - 4) << 2) | 0x01);
+      out[c++] = (uint8_t)dq;
+    } else {
+      out[c++] = (uint8_t)(((piece - 1) << 2) | 0x2);
+      out[c++] = (uint8_t)dq;
+      out[c++] = (uint8_t)(dq >> 8);
+    }
+    len -= piece;
+  }
+  return c;
+}
+
+static size_t team_model(const uint8_t* in, uint32_t n, uint8_t* out, size_t c, int hash_log, emit_fn emit)
 {
   static uint32_t table[1 << 16]; /* position + 1; 0 = empty */
   static uint16_t d[65536];
-  const uint32_t n = (uint32_t)n_;
-  if (n == 0 || n > 65536) return 0;
   memset(table, 0, sizeof(uint32_t) << hash_log);
   const uint32_t npos = n >= 12 ? n - 11 : 0;
   const uint32_t E = n >= 5 ? n - 5 : 0; /* matches end at or before n - 5 */
@@ -70,7 +130,6 @@ size_t lz4_team_model_compress(const uint8_t* in, size_t n_, uint8_t* out, int h
       }
     }
   }
-  size_t c = 0;          /* bytes written */
   uint32_t X = 0, L = 0; /* largest match end seen; first literal not yet written */
   for (uint32_t b0 = 0; b0 < npos; b0 += BLK) {
     const uint32_t bend = b0 + BLK < npos ? b0 + BLK : npos;
@@ -94,26 +153,31 @@ size_t lz4_team_model_compress(const uint8_t* in, size_t n_, uint8_t* out, int h
       }
       const uint32_t s = q > X ? q : X;
       if (m >= s + 4) {
-        const uint32_t nlit = s - L, ml = m - s - 4;
-        out[c++] = (uint8_t)(((nlit >= 15 ? 15 : nlit) << 4) | (ml >= 15 ? 15 : ml));
-        if (nlit >= 15) c = put_lsic(out, c, nlit - 15);
-        memcpy(out + c, in + L, nlit);
-        c += nlit;
-        out[c++] = (uint8_t)(dq & 0xff);
-        out[c++] = (uint8_t)(dq >> 8);
-        if (ml >= 15) c = put_lsic(out, c, ml - 15);
+        c = emit(out, c, in, L, s, m, dq);
         L = m;
       }
       if (m > X) X = m;
       p = m; /* m >= q + 4 */
     }
   }
-  const uint32_t nlit = n - L;
-  out[c++] = (uint8_t)((nlit >= 15 ? 15 : nlit) << 4);
-  if (nlit >= 15) c = put_lsic(out, c, nlit - 15);
-  memcpy(out + c, in + L, nlit);
-  c += nlit;
-  return c;
+  return emit(out, c, in, L, n, n, 0);
+}
+
+size_t lz4_team_model_compress(const uint8_t* in, size_t n, uint8_t* out, int hash_log)
+{
+  if (n == 0 || n > 65536) return 0;
+  return team_model(in, (uint32_t)n, out, 0, hash_log, lz4_emit);
+}
+
+size_t snappy_team_model_compress(const uint8_t* in, size_t n, uint8_t* out, int hash_log)
+{
+  if (n > 65536) return 0;
+  size_t c = 0;
+  uint32_t v = (uint32_t)n; /* preamble: uncompressed length as a varint */
+  while (v >= 0x80) { out[c++] = (uint8_t)(v | 0x80); v >>= 7; }
+  out[c++] = (uint8_t)v;
+  if (n == 0) return c;
+  return team_model(in, (uint32_t)n, out, c, hash_log, snappy_emit);
 }
 
 void lz4_team_model_compress_batch(const uint8_t* in, const size_t* in_off, const size_t* in_bytes, size_t batch,

@@ -20,7 +20,7 @@ CANNOT_DECOMPRESS = 12
 
 def build():
     srcs = [os.path.join(_ORACLE_DIR, f)
-            for f in ("cascaded_oracle.c", "lz4_oracle.c", "snappy_oracle.c", "lz4_team_model.c", "Makefile")]
+            for f in ("cascaded_oracle.c", "lz4_oracle.c", "snappy_oracle.c", "lz_team_model.c", "Makefile")]
     if os.path.exists(_SO) and all(os.path.getmtime(_SO) >= os.path.getmtime(s) for s in srcs):
         return _SO
     subprocess.check_call(["make", "-C", _ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
@@ -52,6 +52,8 @@ def lib():
         L.lz4_oracle_decompress.argtypes = [vp, sz, vp, sz, C.c_int, C.POINTER(sz)]
         L.lz4_team_model_compress.restype = sz
         L.lz4_team_model_compress.argtypes = [vp, sz, vp, C.c_int]
+        L.snappy_team_model_compress.restype = sz
+        L.snappy_team_model_compress.argtypes = [vp, sz, vp, C.c_int]
         L.snappy_oracle_max_compressed.restype = sz
         L.snappy_oracle_max_compressed.argtypes = [sz]
         L.snappy_oracle_compress.restype = sz
@@ -120,7 +122,7 @@ def lz4_team_hash_log(max_chunk):
 
 
 def lz4_team_compress(data, max_chunk=None):
-    """b200comp's own encoder policy for chunks <= 64 KiB (oracle/lz4_team_model.c)."""
+    """b200comp's own encoder policy for chunks <= 64 KiB (oracle/lz_team_model.c)."""
     a = _buf(data)
     assert len(a) <= 65536
     out = np.zeros(lz4_max_compressed(len(a)) + 16, dtype=np.uint8)
@@ -153,6 +155,22 @@ def snappy_compress(data):
     out = np.zeros(snappy_max_compressed(len(a)) + 16, dtype=np.uint8)
     n = lib().snappy_oracle_compress(_p(a), len(a), _p(out))
     return out[:n].copy()
+
+
+def snappy_team_compress(data, max_chunk=None):
+    """b200comp's own Snappy encoder policy for chunks <= 64 KiB (oracle/lz_team_model.c)."""
+    a = _buf(data)
+    assert len(a) <= 65536
+    out = np.zeros(snappy_max_compressed(len(a)) + 16, dtype=np.uint8)
+    n = lib().snappy_team_model_compress(_p(a), len(a), _p(out), lz4_team_hash_log(max_chunk or max(len(a), 1)))
+    return out[:n].copy()
+
+
+def snappy_product_compress(data, max_chunk=None):
+    """The stream libhipcomp.so is expected to produce: team policy up to 64 KiB declared chunk size, the
+    reference's policy above (or when the caller declares no maximum)."""
+    mc = max_chunk if max_chunk is not None else max(len(_buf(data)), 1)
+    return snappy_team_compress(data, mc) if 0 < mc <= 65536 else snappy_compress(data)
 
 
 def snappy_get_size(comp):

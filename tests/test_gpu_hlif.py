@@ -65,7 +65,7 @@ def oracle_encode(kind, chunk, opts=None, max_chunk=None):
     if kind == "lz4":
         return o.lz4_product_compress(chunk, 1, max_chunk)
     if kind == "snappy":
-        return o.snappy_compress(chunk)
+        return o.snappy_product_compress(chunk, max_chunk)
     return o.casc_compress(chunk, opts.type, opts.num_RLEs, opts.num_deltas, opts.use_bp)
 
 

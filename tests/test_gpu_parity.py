@@ -30,7 +30,7 @@ def ragged_chunks(max_size, n, seed):
 @pytest.mark.parametrize("max_chunk", [4096, 16384, 65536])
 def test_lz4_team_encoder_bit_exact_with_model(tsize, type_id, max_chunk):
     """Chunks <= 64 KiB: the stream is byte-identical to the sequential statement of our own policy
-    (oracle/lz4_team_model.c), decodes with liblz4 and with the reference-policy oracle decoder, and is never
+    (oracle/lz_team_model.c), decodes with liblz4 and with the reference-policy oracle decoder, and is never
     larger than GetMaxOutputChunkSize."""
     from test_oracle_lz4 import stock_decompress
 
@@ -121,17 +121,43 @@ def test_lz4_corrupt_input_matches_oracle_and_never_faults():
 
 
 # ------------------------------------------------------------------ Snappy
-@pytest.mark.parametrize("max_chunk", [4096, 65536])
+@pytest.mark.parametrize("max_chunk", [4096, 16384, 65536, 1 << 20])
 def test_snappy_bit_exact_with_oracle(max_chunk):
+    """Chunks <= 64 KiB: byte-identical to the sequential statement of our own policy (oracle/lz_team_model.c);
+    above: to the reference-policy oracle.  Every stream decodes with stock snappy and fits GetMaxOutputChunkSize."""
+    import pyarrow as pa
+
+    stock = pa.Codec("snappy")
     g = _g()
     chunks = ragged_chunks(max_chunk, 48, 2000 + max_chunk) + datagen.mixed_chunks(max_chunk, 12, 78)
     comp, dec, status, sizes, actual = g.roundtrip("snappy", chunks, max_chunk=max_chunk)
     for i, c in enumerate(chunks):
-        exp = o.snappy_compress(c)
+        exp = o.snappy_product_compress(c, max_chunk)
         assert comp[i].tobytes() == exp.tobytes(), f"chunk {i} (len {len(c)}) compressed stream differs"
+        assert len(comp[i]) <= o.snappy_max_compressed(max_chunk)
         assert sizes[i] == len(c)
         if len(c):
             assert status[i] == 0 and actual[i] == len(c) and dec[i].tobytes() == c.tobytes()
+            assert stock.decompress(comp[i].tobytes(), decompressed_size=len(c)).to_pybytes() == c.tobytes()
+
+
+@pytest.mark.parametrize("kind", ["logs", "text", "ints", "zeros", "random", "line37"])
+def test_snappy_team_encoder_ratio_vs_reference_policy(kind):
+    """North star: compression ratio within 1 % of the reference encoder on every input class (reference policy =
+    oracle/snappy_oracle.c, byte-identical to the reference GPU encoder)."""
+    g = _g()
+    n, cb = 2 << 20, 65536
+    rng = np.random.default_rng(11)
+    raw = {"logs": lambda: datagen.log_lines(n, 21), "text": lambda: datagen.zipf_text(n, 22),
+           "ints": lambda: datagen.sorted_ints(n // 4, 23).view(np.uint8), "zeros": lambda: np.zeros(n, np.uint8),
+           "random": lambda: rng.integers(0, 256, n, dtype=np.uint8),
+           "line37": lambda: np.frombuffer((b"the quick brown fox jumps over a dog\n" * (n // 37 + 1))[:n], np.uint8)}[kind]()
+    chunks = [raw[i : i + cb] for i in range(0, n, cb)]
+    comp, dec, status, sizes, actual = g.roundtrip("snappy", chunks, max_chunk=cb)
+    ours = sum(len(c) for c in comp)
+    ref = sum(len(o.snappy_compress(c)) for c in chunks)
+    assert all(d.tobytes() == c.tobytes() for d, c in zip(dec, chunks)) and (status == 0).all()
+    assert n / ours >= 0.99 * (n / ref), f"{kind}: ratio {n / ours:.4f} vs reference policy {n / ref:.4f}"
 
 
 def test_snappy_reference_golden_and_unusual_streams():

@@ -105,7 +105,7 @@ def test_ratio_close_to_liblz4():
 @pytest.mark.parametrize("size", [1, 4, 5, 11, 12, 13, 14, 31, 32, 33, 64, 255, 1000, 1023, 1024, 1025, 2048, 4096, 5000,
                                   16384, 40000, 65535, 65536])
 def test_team_model_streams_are_lz4_blocks(size):
-    """oracle/lz4_team_model.c (the sequential statement of the CUDA team encoder) emits plain LZ4 blocks:
+    """oracle/lz_team_model.c (the sequential statement of the CUDA team encoder) emits plain LZ4 blocks:
     liblz4 and the reference-policy oracle decoder decode them, and they fit GetMaxOutputChunkSize."""
     for chunk in datagen.mixed_chunks(size, 6, 300 + size):
         comp = o.lz4_team_compress(chunk, size)

@@ -120,3 +120,30 @@ def test_ratio_close_to_stock_snappy():
     ours = sum(len(o.snappy_compress(raw[i : i + 65536])) for i in range(0, len(raw), 65536))
     stock = sum(len(CODEC.compress(raw[i : i + 65536].tobytes())) for i in range(0, len(raw), 65536))
     assert ours < 1.35 * stock
+
+
+@pytest.mark.parametrize("size", [0, 1, 4, 5, 11, 12, 13, 60, 61, 64, 255, 256, 257, 1024, 1025, 5000, 16384, 65535, 65536])
+def test_team_model_streams_are_snappy_streams(size):
+    """oracle/lz_team_model.c (the sequential statement of the CUDA team encoder) emits plain Snappy streams:
+    stock snappy and the reference-grammar oracle decoder decode them, and they fit GetMaxOutputChunkSize."""
+    import pyarrow as pa
+
+    stock = pa.Codec("snappy")
+    for chunk in datagen.mixed_chunks(max(size, 1), 6, 400 + size):
+        chunk = chunk[:size]
+        comp = o.snappy_team_compress(chunk, max(size, 1))
+        assert 0 < len(comp) <= o.snappy_max_compressed(size)
+        assert o.snappy_get_size(comp) == size
+        if size:
+            assert stock.decompress(comp.tobytes(), decompressed_size=size).to_pybytes() == chunk.tobytes()
+            st, out = o.snappy_decompress(comp, size)
+            assert st == o.SUCCESS and out.tobytes() == chunk.tobytes()
+
+
+def test_team_model_ratio_not_below_reference_policy():
+    for gen, seed in ((datagen.log_lines, 5), (datagen.zipf_text, 6)):
+        raw = gen(1 << 20, seed)
+        chunks = [raw[i : i + 65536] for i in range(0, len(raw), 65536)]
+        team = sum(len(o.snappy_team_compress(c, 65536)) for c in chunks)
+        ref = sum(len(o.snappy_compress(c)) for c in chunks)
+        assert team <= ref * 1.01
