@@ -50,6 +50,11 @@ for _c, _opts in (("LZ4", LZ4Opts), ("Snappy", SnappyOpts), ("Cascaded", Cascade
 _vpp = C.POINTER(C.c_void_p)
 EXT_PROTOTYPES = {
     "b200compGatherChunksAsync": [_vp, _vp, _vp, _vp, _sz, _vp],
+    "b200compHostAlloc": [_sz, _vpp],
+    "b200compStagerCreate": [C.c_int, _sz, _sz, _vp, C.c_int, _vpp],
+    "b200compStagerCompress": [_vp, _vp, _sz, _vp, _vp, _szp],
+    "b200compStagerDecompress": [_vp, _vp, _vp, _sz, _vp, _sz, _vp],
+    "b200compStagerRoundTrip": [_vp, _vp, _sz, _vp, _vp, _vp, _vp, _szp],
     "b200compManagerCreateLZ4": [_sz, C.c_int, _vp, C.c_int, _vpp],
     "b200compManagerCreateSnappy": [_sz, _vp, C.c_int, _vpp],
     "b200compManagerCreateCascaded": [C.POINTER(CascadedOpts), _vp, C.c_int, _vpp],
@@ -72,6 +77,8 @@ EXT_PROTOTYPES = {
     "b200compDecompConfigStatus": [_vp],
 }
 EXT_VOID = {
+    "b200compHostFree": [_vp],
+    "b200compStagerDestroy": [_vp],
     "b200compManagerDestroy": [_vp],
     "b200compCompConfigDestroy": [_vp],
     "b200compDecompConfigDestroy": [_vp],

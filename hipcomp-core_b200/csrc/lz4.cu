@@ -728,6 +728,12 @@ __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_byt
 //      width by declared chunk size; oracle/lz_team_model.c is called with the same hash_log by the tests.
 constexpr size_t kTeamMaxChunk = 65536;
 
+inline size_t compress_temp_bytes(size_t max_chunk, size_t batch)
+{
+  if (max_chunk <= kTeamMaxChunk) return batch ? 8 : 0;
+  return hash_table_size(max_chunk) * sizeof(uint16_t) * batch;
+}
+
 struct TeamEmit {
   static constexpr bool kNeedDist = false;
   static __device__ __forceinline__ uint32_t lsic_bytes(uint32_t x) { return x >= 15u ? (x - 15u) / 255u + 1u : 0u; }
@@ -804,9 +810,9 @@ hipcompStatus_t hipcompBatchedLZ4CompressGetTempSize(size_t batch_size, size_t m
   B200_CHECK_NOT_NULL(temp_bytes, fn);
   if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
     return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
-  // Same figure as the reference so callers' allocations stay valid; the hash
-  // tables themselves live in shared memory and the workspace is not touched.
-  *temp_bytes = lz4::hash_table_size(max_uncompressed_chunk_bytes) * sizeof(uint16_t) * batch_size;
+  // Chunks up to 64 KiB keep their hash table in shared memory (team encoder): no workspace.  Above, the
+  // reference's figure (a uint16 table per chunk, LZ4CompressionKernels.hip:142-156).
+  *temp_bytes = lz4::compress_temp_bytes(max_uncompressed_chunk_bytes, batch_size);
   return hipcompSuccess;
 }
 
@@ -832,7 +838,7 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
   if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
     return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
   const uint32_t ht = (uint32_t)lz4::hash_table_size(max_uncompressed_chunk_bytes);
-  const size_t required = batch_size * ht * sizeof(uint16_t);
+  const size_t required = lz4::compress_temp_bytes(max_uncompressed_chunk_bytes, batch_size);
   if (temp_bytes < required)
     return fail(hipcompErrorInvalidValue, fn,
                 "Insufficient temp space: got " + std::to_string(temp_bytes) + " bytes, but need "

@@ -26,6 +26,30 @@ hipcompStatus_t b200compGatherChunksAsync(
     hipStream_t stream);
 
 
+/* ---- Host-buffer staging pipeline (no reference counterpart: reference CHANGELOG.md:97-98 leaves
+ * host <-> device staging to the caller).  One call per direction for data that lives in pinned host memory:
+ * the buffer is cut into `slices` that overlap H2D copies, codec kernels and D2H traffic on three streams.
+ * codec: 0 LZ4, 1 Snappy, 2 Cascaded; opts: pointer to that codec's hipcompBatched*Opts_t (NULL = defaults).
+ * Host buffers must be pinned and mapped (b200compHostAlloc, or cudaHostRegister'ed by the caller): the
+ * compressed chunks are packed straight into host_blob by the device.  Chunk i of the blob starts at the sum
+ * of host_comp_sizes[0..i).  Calls block until the host buffers are complete. */
+typedef struct b200compStager b200compStager;
+hipcompStatus_t b200compHostAlloc(size_t bytes, void** out);
+void b200compHostFree(void* p);
+hipcompStatus_t b200compStagerCreate(int codec, size_t chunk_bytes, size_t max_bytes, const void* opts, int slices,
+                                     b200compStager** out);
+void b200compStagerDestroy(b200compStager* s);
+hipcompStatus_t b200compStagerCompress(b200compStager* s, const void* host_raw, size_t nbytes, void* host_blob,
+                                       size_t* host_comp_sizes, size_t* total_comp_bytes);
+hipcompStatus_t b200compStagerDecompress(b200compStager* s, const void* host_blob, const size_t* host_comp_sizes,
+                                         size_t nchunks, void* host_raw_out, size_t nbytes,
+                                         hipcompStatus_t* host_statuses);
+/* compress + decompress of the same buffer, slice k's decompression (from the host copy of its compressed
+ * chunks) queued right behind its compression so both PCIe directions stay busy */
+hipcompStatus_t b200compStagerRoundTrip(b200compStager* s, const void* host_raw, size_t nbytes, void* host_blob,
+                                        size_t* host_comp_sizes, void* host_raw_out, hipcompStatus_t* host_statuses,
+                                        size_t* total_comp_bytes);
+
 /* ---- C view of the high-level managers (hipcomp.hpp classes), for C / FFI callers.
  * A manager handle wraps hipcomp::LZ4Manager / SnappyManager / CascadedManager or the
  * result of hipcomp::create_manager(); a config handle wraps CompressionConfig /

@@ -20,7 +20,7 @@ CANNOT_DECOMPRESS = 12
 
 def build():
     srcs = [os.path.join(_ORACLE_DIR, f)
-            for f in ("cascaded_oracle.c", "lz4_oracle.c", "snappy_oracle.c", "lz_team_model.c", "Makefile")]
+            for f in ("cascaded_oracle.c", "lz4_oracle.c", "snappy_oracle.c", "lz_team_model.c", "cpu_bench.c", "Makefile")]
     if os.path.exists(_SO) and all(os.path.getmtime(_SO) >= os.path.getmtime(s) for s in srcs):
         return _SO
     subprocess.check_call(["make", "-C", _ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)

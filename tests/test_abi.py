@@ -56,7 +56,9 @@ def test_lz4_sizes(n):
     ht = 1
     while ht < n:
         ht *= 2
-    assert out.value == 7 * min(ht, 16384) * 2  # LZ4CompressionKernels.hip:142-156,287-296
+    ref = 7 * min(ht, 16384) * 2  # LZ4CompressionKernels.hip:142-156,287-296
+    # never more than the reference asks for (callers' allocations stay valid); chunks <= 64 KiB need no workspace
+    assert out.value == (ref if n > 65536 else 8)
     assert lib.hipcompBatchedLZ4DecompressGetTempSize(5, n, C.byref(out)) == 0
     assert out.value == 120  # roundUp8(24 * chunks)
 
