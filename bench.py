@@ -1,13 +1,18 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the batched codec hot path (see DESIGN.md "Measurement").
 
-Workload (BASELINE.json configs[1]): LZ4 batched compress + decompress, 64 KiB chunks of
-1 GiB synthetic log text per GPU.  One step = one CompressAsync over the whole batch followed
-by one DecompressAsync of its output.  metric = uncompressed GB (1e9 B) per second through that
-round trip, whole job (all ranks).  Chunks are independent: ranks shard the batch, there is no
-data-path collective ("scaling": "weak": every rank owns its own 1 GiB).
+Default run (`python bench.py [--gpus N]`): the three codecs of the metric, each on its BASELINE.json config,
+  C2  LZ4      64 KiB chunks of 1 GiB synthetic log text per GPU      -> the line's `value`
+  C1  Snappy   64 KiB chunks of 256 MiB mixed-entropy text            -> `codecs.snappy`
+  C3  Cascaded RLE=1 delta=1 bitpack on 4 GiB of sorted int32         -> `codecs.cascaded`
+One step = one CompressAsync over the whole batch followed by one DecompressAsync of its output.
+metric = uncompressed GB (1e9 B) per second through that round trip, whole job (all ranks).  Chunks are
+independent: every rank owns its own buffer ("scaling": "weak"), there is no data-path collective.
+`e2e` is the same round trip from pinned host buffers through the library's staging pipeline
+(b200compStagerRoundTrip), all PCIe traffic inside the timed region.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--codec lz4|snappy|cascaded]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference|refgpu] [--codec lz4|snappy|cascaded]
+  python bench.py --workload c4 [--gpus N]     C4: LZ4 decompress-only, 4 Mi x 4 KiB chunks, strong scaling
 """
 import argparse
 import ctypes as C
@@ -37,16 +42,21 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "refgpu"],
                     help="b200: this library; reference: the CPU codecs on the host cores; refgpu: the reference's "
                          "own GPU build (oracle/_ref/libhipcomp_ref.so) through the same ABI, for context")
-    ap.add_argument("--codec", default="lz4", choices=["lz4", "snappy", "cascaded"])
+    ap.add_argument("--codec", default=None, choices=["lz4", "snappy", "cascaded"],
+                    help="one codec only (default: LZ4 as the line's value, Snappy and Cascaded as codecs.*)")
+    ap.add_argument("--workload", default="default", choices=["default", "c4"])
     ap.add_argument("--size-mib", type=int, default=None, help="uncompressed MiB per GPU (default: the BASELINE config)")
     ap.add_argument("--chunk", type=int, default=None)
-    ap.add_argument("--cpu-sample-mib", type=int, default=None)
+    ap.add_argument("--cpu-sample-mib", type=int, default=None, help="bound the CPU arm's buffer (default: the full config)")
+    ap.add_argument("--cpu-threads", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--data", default="default", choices=["default", "zeros", "random", "text", "logs", "ints"],
                     help="input class (C5 sweep); default = the codec's BASELINE config generator")
     ap.add_argument("--casc-opts", default="1,1,1", help="cascaded num_RLEs,num_deltas,use_bp (C3 = 1,1,1; library default 2,1,1)")
-    ap.add_argument("--e2e-slices", type=int, default=4, help="slices the e2e path pipelines over its streams")
+    ap.add_argument("--casc-type", default="int", choices=["char", "short", "int", "longlong"])
+    ap.add_argument("--e2e-slices", type=int, default=16, help="slices the staging pipeline cuts the buffer into")
+    ap.add_argument("--e2e-mib", type=int, default=1024, help="upper bound on the e2e buffer per GPU (pinned host memory)")
     return ap.parse_args()
 
 
@@ -59,115 +69,138 @@ WORKLOADS = {
     "cascaded": dict(name="C3: Cascaded RLE=1 delta=1 bitpack, 4 GiB int32 sorted column, 64 KiB partitions",
                      size_mib=4096, chunk=65536, seed=0xB203, gen="sorted_ints"),
 }
+CASC_TYPES = {"char": (0, 1), "short": (2, 2), "int": (4, 4), "longlong": (6, 8)}  # hipcompType_t id, element bytes
+
+
+def workload_for(args, codec):
+    """The BASELINE config of `codec` with the command line's overrides; the name says what was overridden."""
+    wl = dict(WORKLOADS[codec])
+    base = dict(wl)
+    if args.size_mib:
+        wl["size_mib"] = args.size_mib
+    if args.chunk:
+        wl["chunk"] = args.chunk
+    notes = []
+    if wl["size_mib"] != base["size_mib"]:
+        notes.append(f"{wl['size_mib']} MiB per GPU")
+    if wl["chunk"] != base["chunk"]:
+        notes.append(f"{wl['chunk']} B chunks")
+    if args.data != "default":
+        notes.append(f"input class {args.data}")
+    if codec == "cascaded" and args.casc_opts != "1,1,1":
+        notes.append(f"opts {args.casc_opts}")
+    if codec == "cascaded" and args.casc_type != "int":
+        notes.append(f"type {args.casc_type}")
+    if notes:
+        wl["name"] = f"{codec} (derived from {base['name'].split(':')[0]}): " + ", ".join(notes)
+    return wl
+
+
+def make_config(wl, world, nbytes, nchunks):
+    return {"workload": wl["name"], "bytes_per_gpu": nbytes, "chunk_bytes": wl["chunk"], "chunks_per_gpu": nchunks,
+            "sharding": f"{world} rank(s), independent chunk ranges, no collective",
+            "l2": "inputs (>= 256 MiB per step) larger than the 126 MB L2; no explicit flush", "seed": wl["seed"]}
 
 
 # ----------------------------------------------------------------------------- CPU codecs
 class CpuCodec:
     """The CPU implementation timed as the reference arm / cpu_baseline.
 
-    lz4     : liblz4.so.1 LZ4_compress_default / LZ4_decompress_safe (the CPU LZ4 block codec the
-              north_star names; the reference ships none of its own)
-    snappy  : the snappy bundled with pyarrow (stand-in for share/snappy's python-snappy dependency)
-    cascaded: oracle/cascaded_oracle.c (CPU restatement; no other CPU implementation exists)
-    Chunks are spread over all host threads; ctypes / pyarrow release the GIL inside the codec calls.
+    lz4     : liblz4.so.1 LZ4_compress_default / LZ4_decompress_safe (the CPU LZ4 block codec the north_star
+              names; the reference ships none of its own), driven by oracle/cpu_bench.c (pthreads, clock_gettime)
+    cascaded: oracle/cascaded_oracle.c (CPU restatement; no other CPU implementation exists), same C harness
+    snappy  : the snappy bundled with pyarrow (stand-in for share/snappy's python-snappy dependency; hidden
+              symbols, so it is driven from Python threads - pyarrow releases the GIL inside the codec)
     """
 
-    def __init__(self, codec, chunk):
+    def __init__(self, codec, chunk, casc=None, threads=None):
         self.codec, self.chunk = codec, chunk
-        self.threads = os.cpu_count() or 1
-        if codec == "lz4":
-            self.lib = C.CDLL("liblz4.so.1")
-            self.lib.LZ4_compress_default.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
-            self.lib.LZ4_decompress_safe.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
-            self.bound = self.lib.LZ4_compressBound(chunk)
-            self.kind, self.desc = "reference", "liblz4.so.1 LZ4_compress_default+LZ4_decompress_safe"
-        elif codec == "snappy":
+        self.threads = threads or os.cpu_count() or 1
+        self.casc = casc  # (type id, rle, delta, bp, width)
+        if codec == "snappy":
             import pyarrow as pa
 
             self.pa = pa.Codec("snappy")
-            self.kind, self.desc = "reference", "stock snappy (pyarrow bundled) compress+decompress"
+            self.kind, self.desc = "reference", "stock snappy (pyarrow bundled), Python threads"
         else:
             sys.path.insert(0, os.path.join(ROOT, "tests"))
             import oracle_lib
 
-            self.o = oracle_lib
-            self.o.lib()
-            self.kind, self.desc = "port", "oracle/cascaded_oracle.c compress+decompress (RLE=1,delta=1,bp=1)"
+            self.lib = oracle_lib.lib()
+            self.lib.cpu_bench_run.restype = C.c_int
+            self.lib.cpu_bench_run.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
+                                               C.POINTER(C.c_int), C.POINTER(C.c_double)]
+            if codec == "lz4":
+                self.kind, self.desc = "reference", "liblz4.so.1 LZ4_compress_default+LZ4_decompress_safe, C pthreads harness"
+            else:
+                self.kind, self.desc = "port", "oracle/cascaded_oracle.c compress+decompress, C pthreads harness"
 
-    def _run_threads(self, fn, n):
-        T = min(self.threads, n)
-        errs = []
+    def roundtrip_seconds(self, raw, threads=None, passes=1):
+        """raw: np.uint8 array.  Returns (t_compress, t_decompress, compressed_bytes of one pass)."""
+        T = threads or self.threads
+        if self.codec != "snappy":
+            out = (C.c_double * 3)()
+            casc = (C.c_int * 5)(*(self.casc or (4, 1, 1, 1, 4)))
+            rc = self.lib.cpu_bench_run(0 if self.codec == "lz4" else 2, raw.ctypes.data, raw.size, self.chunk, T, passes,
+                                        casc, out)
+            if rc != 0:
+                raise RuntimeError(f"cpu_bench_run -> {rc}")
+            return out[0], out[1], int(out[2])
+        n, ch = (len(raw) + self.chunk - 1) // self.chunk, self.chunk
+        comp = [None] * n
+        mv = memoryview(raw)
 
-        def work(k):
-            try:
-                for i in range(k, n, T):
-                    fn(i)
-            except Exception as e:  # pragma: no cover
-                errs.append(e)
+        def run(fn):
+            errs = []
 
-        ts = [threading.Thread(target=work, args=(k,)) for k in range(T)]
-        t0 = time.perf_counter()
-        for t in ts:
-            t.start()
-        for t in ts:
-            t.join()
-        dt = time.perf_counter() - t0
-        if errs:
-            raise errs[0]
-        return dt
+            def work(k):
+                try:
+                    for i in range(k, n, T):
+                        fn(i)
+                except Exception as e:  # pragma: no cover
+                    errs.append(e)
 
-    def roundtrip_seconds(self, raw):
-        """raw: np.uint8 array, multiple of chunk.  Returns (t_compress, t_decompress, compressed_bytes)."""
-        n, ch = len(raw) // self.chunk, self.chunk
-        if self.codec == "lz4":
-            comp = np.empty((n, self.bound), np.uint8)
-            sizes = np.zeros(n, np.int64)
-            back = np.empty_like(raw)
-            rp, cp, bp = raw.ctypes.data, comp.ctypes.data, back.ctypes.data
-            lib, bound = self.lib, self.bound
-
-            def enc(i):
-                sizes[i] = lib.LZ4_compress_default(rp + i * ch, cp + i * bound, ch, bound)
-
-            def dec(i):
-                if lib.LZ4_decompress_safe(cp + i * bound, bp + i * ch, int(sizes[i]), ch) != ch:
-                    raise RuntimeError("liblz4 round trip failed")
-
-            tc = self._run_threads(enc, n)
-            td = self._run_threads(dec, n)
-            assert back[: ch * 4].tobytes() == raw[: ch * 4].tobytes()
-            return tc, td, int(sizes.sum())
-        if self.codec == "snappy":
-            comp = [None] * n
-            mv = memoryview(raw)
-
-            def enc(i):
-                comp[i] = self.pa.compress(mv[i * ch : (i + 1) * ch])
-
-            def dec(i):
-                self.pa.decompress(comp[i], decompressed_size=ch)
-
-            tc = self._run_threads(enc, n)
-            td = self._run_threads(dec, n)
-            return tc, td, sum(c.size for c in comp)
-        L = self.o.lib()
-        stride = ch + 16
-        comp = np.zeros((n, stride), np.uint8)
-        sizes = np.zeros(n, np.int64)
-        back = np.empty_like(raw)
-        rp, cp, bp = raw.ctypes.data, comp.ctypes.data, back.ctypes.data
+            ts = [threading.Thread(target=work, args=(k,)) for k in range(min(T, n))]
+            t0 = time.perf_counter()
+            for _ in range(passes):
+                for t in ts:
+                    t.start()
+                for t in ts:
+                    t.join()
+                ts = [threading.Thread(target=work, args=(k,)) for k in range(min(T, n))]
+            dt = time.perf_counter() - t0
+            if errs:
+                raise errs[0]
+            return dt
 
         def enc(i):
-            sizes[i] = L.casc_oracle_compress(rp + i * ch, ch, cp + i * stride, 4, 1, 1, 1)
+            comp[i] = self.pa.compress(mv[i * ch:(i + 1) * ch])
 
         def dec(i):
-            a = C.c_size_t(0)
-            if L.casc_oracle_decompress(cp + i * stride, int(sizes[i]), bp + i * ch, ch, 4, C.byref(a)) != 0:
-                raise RuntimeError("oracle round trip failed")
+            self.pa.decompress(comp[i], decompressed_size=min(ch, len(raw) - i * ch))
 
-        tc = self._run_threads(enc, n)
-        td = self._run_threads(dec, n)
-        return tc, td, int(sizes.sum())
+        tc = run(enc)
+        td = run(dec)
+        return tc, td, sum(c.size for c in comp)
+
+    def baseline(self, raw, passes=1, steps=1, with_single=True):
+        """cpu_baseline record: all threads over `raw` (x passes) per step, plus a 1-thread row on a bounded sample."""
+        tcs, tds, cb = [], [], 0
+        for _ in range(steps):
+            tc, td, cb = self.roundtrip_seconds(raw, passes=passes)
+            tcs.append(tc)
+            tds.append(td)
+        tot = len(raw) * passes * steps
+        rec = {"value": tot / (sum(tcs) + sum(tds)) / GB, "unit": "GB/s", "cores": self.threads, "kind": self.kind,
+               "sample": f"{len(raw) >> 20} MiB of the same workload x {passes} pass(es) per step, {self.desc}, {self.threads} threads",
+               "compress_GBps": tot / sum(tcs) / GB, "decompress_GBps": tot / sum(tds) / GB,
+               "compression_ratio": len(raw) / max(cb, 1), "seconds_per_step": (sum(tcs) + sum(tds)) / steps}
+        if with_single:
+            small = raw[: min(len(raw), 64 << 20)]
+            tc, td, _ = self.roundtrip_seconds(small, threads=1)
+            rec["single_thread"] = {"value": len(small) / (tc + td) / GB, "compress_GBps": len(small) / tc / GB,
+                                    "decompress_GBps": len(small) / td / GB, "sample": f"first {len(small) >> 20} MiB, 1 thread"}
+        return rec
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -322,14 +355,14 @@ def make_data(args, wl, rank, device):
 class Plan:
     """Pre-allocated buffers + argument lists so the timed loop is just the two C-ABI calls."""
 
-    def __init__(self, codec, raw, chunk, casc_opts=(1, 1, 1)):
+    def __init__(self, codec, raw, chunk, casc_opts=(1, 1, 1), casc_type=4):
         B = importlib.import_module("hipcomp-core_b200.batched")
         L = importlib.import_module("hipcomp-core_b200._lib")
         self.B, self.L, self.codec, self.chunk = B, L, codec, chunk
         dev = raw.device
         self.n = raw.numel() // chunk
         self.raw = raw
-        self.opts = L.CascadedOpts(4096, L.TYPE_INT, *casc_opts) if codec == "cascaded" else B.default_opts(codec)
+        self.opts = L.CascadedOpts(4096, casc_type, *casc_opts) if codec == "cascaded" else B.default_opts(codec)
         off = np.arange(self.n, dtype=np.int64) * chunk
         self.src = B.DeviceBatch(raw, off, np.full(self.n, chunk, np.int64))
         self.stride = (B.max_compressed_chunk_bytes(codec, chunk, self.opts) + 15) // 16 * 16
@@ -352,25 +385,19 @@ class Plan:
             self.f_gather.restype = C.c_int
             self.f_gather.argtypes = [C.c_void_p] * 4 + [C.c_size_t, C.c_void_p]
 
-    def compress(self, src_ptrs=None, stream=None, lo=0, n=None):
-        """One CompressAsync over chunks [lo, lo+n) (default: the whole batch)."""
-        n = self.n if n is None else n
-        s = C.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
-        per_chunk_temp = self.temp_bytes // max(self.n, 1)
-        st = self.f_comp((src_ptrs if src_ptrs is not None else self.src.ptrs.data_ptr()) + 8 * lo,
-                         self.src.sizes.data_ptr() + 8 * lo, self.chunk, n, self.temp.data_ptr() + per_chunk_temp * lo,
-                         per_chunk_temp * n, self.comp.ptrs.data_ptr() + 8 * lo, self.comp_sizes.data_ptr() + 8 * lo,
-                         self.opts, s)
+    def compress(self):
+        """One CompressAsync over the whole batch."""
+        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        st = self.f_comp(self.src.ptrs.data_ptr(), self.src.sizes.data_ptr(), self.chunk, self.n, self.temp.data_ptr(),
+                         self.temp_bytes, self.comp.ptrs.data_ptr(), self.comp_sizes.data_ptr(), self.opts, s)
         assert st == 0, f"CompressAsync -> {st}"
 
-    def decompress(self, comp_ptrs=None, comp_sizes=None, stream=None, lo=0, n=None):
-        """One DecompressAsync; comp_ptrs / comp_sizes (if given) already start at chunk lo."""
-        n = self.n if n is None else n
-        s = C.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
-        st = self.f_dec(comp_ptrs if comp_ptrs is not None else self.comp.ptrs.data_ptr() + 8 * lo,
-                        comp_sizes.data_ptr() if comp_sizes is not None else self.comp_sizes.data_ptr() + 8 * lo,
-                        self.dst.sizes.data_ptr() + 8 * lo, self.actual.data_ptr() + 8 * lo, n, self.dtemp.data_ptr(),
-                        self.dtemp_bytes, self.dst.ptrs.data_ptr() + 8 * lo, self.status.data_ptr() + 4 * lo, s)
+    def decompress(self):
+        """One DecompressAsync of the compress output."""
+        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        st = self.f_dec(self.comp.ptrs.data_ptr(), self.comp_sizes.data_ptr(), self.dst.sizes.data_ptr(),
+                        self.actual.data_ptr(), self.n, self.dtemp.data_ptr(), self.dtemp_bytes, self.dst.ptrs.data_ptr(),
+                        self.status.data_ptr(), s)
         assert st == 0, f"DecompressAsync -> {st}"
 
     def verify(self):
@@ -380,22 +407,92 @@ class Plan:
         assert torch.equal(self.back, self.raw), "round trip is not bit-exact"
 
 
-def run_b200(args):
-    wl = dict(WORKLOADS[args.codec])
-    if args.size_mib:
-        wl["size_mib"] = args.size_mib
-    if args.chunk:
-        wl["chunk"] = args.chunk
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
-    world, rank, local = dist_setup(args.gpus)
-    torch.cuda.set_device(local)
-    device = torch.device("cuda", local)
+
+
+def copy_ceiling(nbytes, device):
+    """Plain pinned-memory copies of the same size on two streams: what PCIe gives this rank (H2D, D2H, both at once)."""
+    n = min(nbytes, 1 << 30)
+    h_a = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    h_b = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    d_a = torch.empty(n, dtype=torch.uint8, device=device)
+    d_b = torch.empty(n, dtype=torch.uint8, device=device)
+    s1, s2 = torch.cuda.Stream(device), torch.cuda.Stream(device)
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps
+
+    def h2d():
+        with torch.cuda.stream(s1):
+            d_a.copy_(h_a, non_blocking=True)
+
+    def d2h():
+        with torch.cuda.stream(s2):
+            h_b.copy_(d_b, non_blocking=True)
+
+    def both():
+        h2d()
+        d2h()
+
+    t1, t2, t3 = timed(h2d), timed(d2h), timed(both)
+    return {"h2d_GBps": n / t1 / GB, "d2h_GBps": n / t2 / GB, "duplex_GBps_each_way": n / t3 / GB, "bytes": n}
+
+
+def run_e2e(codec, plan, raw, args, world, device, comp_bytes):
+    """Host-resident input -> compressed blob in host memory -> host-resident output, through the library's staging
+    pipeline (b200compStagerRoundTrip, csrc/stager.cu): pinned raw -H2D-> CompressAsync -> chunks packed into the
+    pinned blob by the device + sizes D2H -> blob slice H2D -> DecompressAsync -> D2H raw + statuses.  Every byte
+    makes the whole trip inside the timed region; slices overlap on three streams."""
+    S = importlib.import_module("hipcomp-core_b200.staging")
+    nbytes = min(raw.numel(), args.e2e_mib << 20) // plan.chunk * plan.chunk
+    n = nbytes // plan.chunk
+    st = S.Stager(codec, plan.chunk, nbytes, opts=plan.opts if codec == "cascaded" else None, slices=args.e2e_slices)
+    h_raw, h_back = S.PinnedArray(nbytes), S.PinnedArray(nbytes)
+    h_blob, h_sizes, h_status = S.PinnedArray(n * plan.stride), S.PinnedArray(n, np.uint64), S.PinnedArray(n, np.int32)
+    torch.from_numpy(h_raw.array).copy_(raw[:nbytes])
+    K = max(2, min(args.steps, 5))
+    total = st.roundtrip(h_raw, h_blob, h_sizes, h_back, h_status)  # warm-up + check
+    assert (h_status.array == 0).all() and np.array_equal(h_back.array, h_raw.array), "e2e round trip failed"
+    h_back.array[:] = 0
+    barrier(world)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        total = st.roundtrip(h_raw, h_blob, h_sizes, h_back, h_status)  # blocks until the host buffers are complete
+    t = time.perf_counter() - t0
+    barrier(world)
+    assert (h_status.array == 0).all() and np.array_equal(h_back.array, h_raw.array), "e2e round trip failed"
+    t = max_over_ranks(t, world, device)
+    tot_bytes = sum_over_ranks(float(nbytes), world, device)
+    rec = {"value": tot_bytes * K / t / GB, "unit": "GB/s", "h2d_bytes_per_step": nbytes + total + 16 * n,
+           "d2h_bytes_per_step": total + 8 * n + nbytes + 4 * n, "steps": K, "ms_per_step": t / K * 1e3,
+           "bytes_per_gpu": nbytes, "slices": args.e2e_slices, "streams": 3,
+           "timing": "host wall clock around K blocking library calls (max over ranks)",
+           "path": "b200compStagerRoundTrip: pinned host raw -> H2D -> CompressAsync -> chunks packed into the pinned host "
+                   "blob by the device + sizes D2H -> blob H2D -> DecompressAsync -> D2H raw+statuses; slices pipelined "
+                   "over 3 streams, all copies inside the timed region"}
+    st.close()
+    for a in (h_raw, h_back, h_blob, h_sizes, h_status):
+        a.free()
+    if world == 1:
+        rec["copy_ceiling"] = copy_ceiling(nbytes, device)
+    return rec
+
+
+def measure_codec(args, codec, world, rank, local, device, with_cpu):
+    """Times K steps of `codec` on its workload; returns the record (rank 0) or None."""
+    wl = workload_for(args, codec)
     raw = make_data(args, wl, rank, device)
     nbytes = raw.numel()
     casc_opts = tuple(int(x) for x in args.casc_opts.split(","))
-    plan = Plan(args.codec, raw, wl["chunk"], casc_opts)
+    ctype, cwidth = CASC_TYPES[args.casc_type]
+    plan = Plan(codec, raw, wl["chunk"], casc_opts, ctype)
     ev = lambda: torch.cuda.Event(enable_timing=True)
-
     clocks = ClockSampler(local)
     clocks.start()
     for _ in range(max(args.warmup, 3)):
@@ -404,8 +501,8 @@ def run_b200(args):
     plan.verify()
     comp_bytes = int(plan.comp_sizes.sum().item())
 
-    # ---- timed region: K steps, inputs resident in HBM.  1 GiB input + ~1.4 GiB of other buffers per
-    # step is far larger than the 126 MB L2, so nothing survives in L2 from one step to the next.
+    # ---- timed region: K steps, inputs resident in HBM.  Every step touches >= 256 MiB of input plus its
+    # outputs, far more than the 126 MB L2, so nothing survives in L2 from one step to the next.
     barrier(world)
     torch.cuda.synchronize()
     clocks.mark_begin()
@@ -422,6 +519,7 @@ def run_b200(args):
     clocks.mark_end()
     barrier(world)
     clk = clocks.stop()
+    K = args.steps
     t_comp = sum(a.elapsed_time(b) for a, b, _ in marks) / 1e3
     t_dec = sum(b.elapsed_time(c) for _, b, c in marks) / 1e3
     t_total = marks[0][0].elapsed_time(marks[-1][2]) / 1e3
@@ -431,215 +529,260 @@ def run_b200(args):
     total_bytes = sum_over_ranks(float(nbytes), world, device)
     total_comp = sum_over_ranks(float(comp_bytes), world, device)
     plan.verify()
-
-    # ---- e2e: host buffers in, host buffers out, through the same C-ABI calls
     e2e = None
-    if not args.no_e2e:
-        e2e = run_e2e(plan, raw, args, world, device)
-
+    if not args.no_e2e and args.impl == "b200":
+        e2e = run_e2e(codec, plan, raw, args, world, device, comp_bytes)
     if rank != 0:
-        return
+        return None
     peak, peak_src = load_peaks()
-    K = args.steps
     alg_comp = nbytes + comp_bytes  # compress: raw read + compressed written (per launch, this rank)
     alg_dec = comp_bytes + nbytes
     comp_ms, dec_ms = t_comp / K * 1e3, t_dec / K * 1e3
     dominant = "compress" if t_comp >= t_dec else "decompress"
-    ach = (alg_comp / (t_comp / K) if dominant == "compress" else alg_dec / (t_dec / K)) / GB
-    line = {
-        **({"impl": "refgpu"} if args.impl == "refgpu" else {}),
-        "metric": f"{args.codec}_roundtrip_throughput",
+
+    def roof(direction):
+        alg, ms = (alg_comp, comp_ms) if direction == "compress" else (alg_dec, dec_ms)
+        ach = alg / (ms / 1e3) / GB
+        return {"bound": "hbm", "kernel": f"{codec}::{direction}", "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak, **load_traffic(codec, direction, nbytes), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg, "ms_per_launch": ms}
+
+    launches = {"lz4": 2, "snappy": 2, "cascaded": CASCADED_LAUNCHES_PER_STEP}[codec]
+    rec = {
+        "metric": f"{codec}_roundtrip_throughput",
         "value": total_bytes * K / t_total_max / GB,
         "unit": "GB/s",
-        "n_gpus": world,
-        "steps": K,
-        "warmup": max(args.warmup, 3),
         "ms_per_step": t_total_max / K * 1e3,
-        "higher_is_better": True,
-        "scaling": "weak",
-        "vs_baseline": None,
-        "dtype": "u8" if args.codec != "cascaded" else "int32",
-        "data": "synthetic",
-        "config": {"workload": wl["name"] + ("" if args.data == "default" else f" [input class: {args.data}]")
-                   + ("" if args.codec != "cascaded" or casc_opts == (1, 1, 1) else f" [opts {args.casc_opts}]"),
-                   "bytes_per_gpu": nbytes, "chunk_bytes": wl["chunk"],
-                   "chunks_per_gpu": plan.n, "sharding": f"{world} rank(s), independent chunk ranges, no collective",
-                   "l2": "inputs (>= 1 GiB per step) larger than the 126 MB L2; no explicit flush",
-                   "seed": wl["seed"]},
+        "dtype": "u8" if codec != "cascaded" else {1: "int8", 2: "int16", 4: "int32", 8: "int64"}[cwidth],
+        "config": make_config(wl, world, nbytes, plan.n),
         "compress_GBps": total_bytes * K / t_comp_max / GB,
         "decompress_GBps": total_bytes * K / t_dec_max / GB,
         "compression_ratio": total_bytes / total_comp,
-        "roofline": {"bound": "hbm", "kernel": f"{args.codec}::{dominant}_kernel", "achieved": ach, "peak": peak,
-                     "unit": "GB/s", "frac": ach / peak, **load_traffic(args.codec, dominant, nbytes), "peak_source": peak_src,
-                     "ms_per_launch": comp_ms if dominant == "compress" else dec_ms},
-        "roofline_decompress": {"bound": "hbm", "achieved": alg_dec / (t_dec / K) / GB, "peak": peak, "unit": "GB/s",
-                                "frac": alg_dec / (t_dec / K) / GB / peak, "ms_per_launch": dec_ms},
-        "roofline_compress": {"bound": "hbm", "achieved": alg_comp / (t_comp / K) / GB, "peak": peak, "unit": "GB/s",
-                              "frac": alg_comp / (t_comp / K) / GB / peak, "ms_per_launch": comp_ms},
-        "gpu_launches": 2 * K if args.codec != "cascaded" else 6 * K,  # cascaded: 1 compress + 5 decompress instantiations
+        "roofline": roof(dominant),
+        "roofline_compress": roof("compress"),
+        "roofline_decompress": roof("decompress"),
+        "gpu_launches": launches * K,
         "clocks": clk,
     }
     if e2e:
-        line["e2e"] = e2e
-    if world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline(args, wl, raw)
+        rec["e2e"] = e2e
+    if with_cpu:
+        cpu = CpuCodec(codec, wl["chunk"], casc=(ctype, *casc_opts, cwidth), threads=args.cpu_threads)
+        mib = min(args.cpu_sample_mib or wl["size_mib"], wl["size_mib"])
+        rec["cpu_baseline"] = cpu.baseline(raw[: mib << 20].cpu().numpy())
+    del plan, raw
+    torch.cuda.empty_cache()
+    return rec
+
+
+CASCADED_LAUNCHES_PER_STEP = 6  # 1 compress + 5 decompress instantiations (4 exit after reading partition 0's header)
+
+
+def run_b200(args):
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    world, rank, local = dist_setup(args.gpus)
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    codecs = [args.codec] if args.codec else ["lz4", "snappy", "cascaded"]
+    with_cpu = world == 1 and not args.no_cpu and args.impl == "b200"
+    recs = {}
+    for c in codecs:
+        recs[c] = measure_codec(args, c, world, rank, local, device, with_cpu)
+    if rank != 0:
+        return
+    head = recs[codecs[0]]
+    line = {
+        **({"impl": "refgpu"} if args.impl == "refgpu" else {}),
+        "metric": head["metric"], "value": head["value"], "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": head["dtype"], "data": "synthetic",
+        **{k: head[k] for k in ("config", "compress_GBps", "decompress_GBps", "compression_ratio", "roofline",
+                                "roofline_compress", "roofline_decompress", "gpu_launches", "clocks")},
+    }
+    for k in ("e2e", "cpu_baseline"):
+        if k in head:
+            line[k] = head[k]
+    if len(codecs) > 1:
+        line["codecs"] = {c: recs[c] for c in codecs[1:]}
     print(json.dumps(line), flush=True)
 
 
-def run_e2e(plan, raw, args, world, device):
-    """Host-resident input -> compress -> host-resident compressed blob -> decompress -> host-resident output,
-    through the same C-ABI calls, as a caller with host data would drive them: the batch is cut into slices
-    that travel down three streams, so the H2D copy of one slice, the kernels of another and the D2H copy of a
-    third overlap (PCIe is full duplex).  Every byte still makes the whole trip inside the timed region:
-      pinned raw -H2D-> CompressAsync -> gather -D2H-> pinned blob + sizes -H2D-> DecompressAsync -D2H-> pinned raw
-    The host needs each slice's compressed size before it can size the blob copies: it waits on that slice's
-    event only, while later slices are already queued."""
-    n, chunk, nbytes = plan.n, plan.chunk, raw.numel()
-    S = max(1, min(args.e2e_slices, n))
-    bounds = [n * k // S for k in range(S + 1)]
-    h_raw = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-    h_raw.copy_(raw)
-    h_back = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-    h_sizes = torch.empty(n, dtype=torch.int64, pin_memory=True)
-    h_status = torch.empty(n, dtype=torch.int32, pin_memory=True)
-    h_blob = torch.empty(n * plan.stride, dtype=torch.uint8, pin_memory=True)
-    d_in = torch.empty_like(raw)
-    d_blob = torch.empty(n * plan.stride, dtype=torch.uint8, device=device)
-    d_blob2 = torch.empty_like(d_blob)
-    d_sizes2 = torch.empty(n, dtype=torch.int64, device=device)
-    in_ptrs = torch.from_numpy(np.arange(n, dtype=np.int64) * chunk + d_in.data_ptr()).to(device)
-    streams = [torch.cuda.Stream(device) for _ in range(min(3, S))]
-    K = max(2, min(args.steps, 5))
-    main = torch.cuda.current_stream()
+# ----------------------------------------------------------------------------- C4
+def run_c4(args):
+    """BASELINE.json configs[3]: LZ4 decompress-only of a pre-compressed batch of 4 KiB chunks (4 Mi chunks = 16 GiB
+    by default), STRONG scaling: the batch is fixed, one global compressed-size array goes through
+    sharding.shard_bounds -> every rank decompresses its contiguous, byte-balanced chunk range -> the per-chunk
+    results travel through sharding.gather_sizes (NCCL all_gather; timed on its own).  Setup (untimed): every rank
+    generates and compresses the blocks of its own range and of nothing else; the size array is all-gathered."""
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    world, rank, local = dist_setup(args.gpus)
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    B = importlib.import_module("hipcomp-core_b200.batched")
+    S = importlib.import_module("hipcomp-core_b200.synth")
+    SH = importlib.import_module("hipcomp-core_b200.sharding")
+    chunk = args.chunk or 4096
+    total_mib = args.size_mib or 16384
+    block_mib = 256  # generation unit: block b of the global buffer is log_lines(seed + b), on whichever rank needs it
+    nblocks = total_mib // block_mib
+    cpb = (block_mib << 20) // chunk
+    nchunks = nblocks * cpb
+    stride = (B.max_compressed_chunk_bytes("lz4", chunk, B.default_opts("lz4")) + 15) // 16 * 16
 
-    def stage1(k):
-        lo, hi = bounds[k], bounds[k + 1]
-        st = streams[k % len(streams)]
-        with torch.cuda.stream(st):
-            d_in[lo * chunk:hi * chunk].copy_(h_raw[lo * chunk:hi * chunk], non_blocking=True)
-            plan.compress(src_ptrs=in_ptrs.data_ptr(), stream=st, lo=lo, n=hi - lo)
-            sz = plan.comp_sizes[lo:hi]
-            offs = torch.cumsum(sz, 0) - sz
-            rc = plan.f_gather(plan.comp.ptrs.data_ptr() + 8 * lo, sz.data_ptr(), offs.data_ptr(),
-                               d_blob.data_ptr() + lo * plan.stride, hi - lo, C.c_void_p(st.cuda_stream))
-            assert rc == 0
-            h_sizes[lo:hi].copy_(sz, non_blocking=True)
-            ev = torch.cuda.Event()
-            ev.record(st)
-        return ev, offs
+    def compress_block(b):
+        raw = S.log_lines(block_mib << 20, 0xC400 + b, device)
+        src = B.DeviceBatch(raw, np.arange(cpb, dtype=np.int64) * chunk, np.full(cpb, chunk, np.int64))
+        comp = B.compress("lz4", src, max_chunk=chunk)
+        return raw, comp
 
-    def stage2(k, ev):
-        lo, hi = bounds[k], bounds[k + 1]
-        st = streams[k % len(streams)]
-        ev.synchronize()
-        total = int(h_sizes[lo:hi].sum().item())
-        base = lo * plan.stride
-        with torch.cuda.stream(st):
-            h_blob[base:base + total].copy_(d_blob[base:base + total], non_blocking=True)
-            # decompress direction, from the host copy of the compressed slice
-            d_blob2[base:base + total].copy_(h_blob[base:base + total], non_blocking=True)
-            d_sizes2[lo:hi].copy_(h_sizes[lo:hi], non_blocking=True)
-            sz = d_sizes2[lo:hi]
-            ptrs = torch.cumsum(sz, 0) - sz + (d_blob2.data_ptr() + base)
-            plan.decompress(comp_ptrs=ptrs.data_ptr(), comp_sizes=sz, stream=st, lo=lo, n=hi - lo)
-            h_back[lo * chunk:hi * chunk].copy_(plan.back[lo * chunk:hi * chunk], non_blocking=True)
-            h_status[lo:hi].copy_(plan.status[lo:hi], non_blocking=True)
-        return total, ptrs
+    # pass 1 (untimed): compressed sizes of an even split of the blocks, all-gathered into the global size array
+    blo, bhi = nblocks * rank // world, nblocks * (rank + 1) // world
+    local_sizes = []
+    for b in range(blo, bhi):
+        _, comp = compress_block(b)
+        local_sizes.append(comp.sizes.clone())
+        del comp
+    local_sizes = torch.cat(local_sizes) if local_sizes else torch.zeros(0, dtype=torch.int64, device=device)
+    if world > 1:
+        gsizes, _, _, _ = SH.gather_sizes(local_sizes)
+    else:
+        gsizes = local_sizes.cpu().numpy()
+    assert len(gsizes) == nchunks
+    bounds = SH.shard_bounds(gsizes, world)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    n = hi - lo
+    # pass 2 (untimed): this rank's byte-balanced range, compressed streams packed back to back
+    my_sizes = torch.from_numpy(np.ascontiguousarray(gsizes[lo:hi])).to(device)
+    offs = torch.cumsum(my_sizes, 0) - my_sizes
+    blob = torch.empty(int(my_sizes.sum().item()) + 64, dtype=torch.uint8, device=device)
+    check = torch.zeros(1, dtype=torch.int64, device=device)
+    lib = importlib.import_module("hipcomp-core_b200._lib").lib()
+    for b in range(lo // cpb, (hi + cpb - 1) // cpb if n else 0):
+        raw, comp = compress_block(b)
+        c0, c1 = max(lo, b * cpb), min(hi, (b + 1) * cpb)
+        k0 = c0 - b * cpb
+        rc = lib.b200compGatherChunksAsync(comp.ptrs.data_ptr() + 8 * k0, comp.sizes.data_ptr() + 8 * k0,
+                                           offs.data_ptr() + 8 * (c0 - lo), blob.data_ptr(), c1 - c0,
+                                           C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0
+        check += raw[k0 * chunk:(c1 - b * cpb) * chunk].view(torch.int64).sum()
+        torch.cuda.synchronize()
+        del raw, comp
+    comp_batch = B.DeviceBatch(blob, offs.cpu().numpy(), my_sizes)
+    out = B.DeviceBatch.empty(n, chunk, device)
+    dtemp = torch.empty(max(B.decompress_temp_bytes("lz4", n, chunk), 16), dtype=torch.uint8, device=device)
+    actual = torch.zeros(n, dtype=torch.int64, device=device)
+    status = torch.zeros(n, dtype=torch.int32, device=device)
+    f_dec = lib.hipcompBatchedLZ4DecompressAsync
 
     def step():
-        for st in streams:
-            st.wait_stream(main)
-        depth = len(streams) - 1 if len(streams) > 1 else 0
-        pending, keep, total = [], [], 0
-        for k in range(S + depth):
-            if k < S:
-                pending.append(stage1(k))
-            j = k - depth
-            if j >= 0:
-                ev, offs = pending[j]
-                t, ptrs = stage2(j, ev)
-                total += t
-                keep.append((offs, ptrs))
-        for st in streams:
-            main.wait_stream(st)
-        main.synchronize()
-        return total
+        st = f_dec(comp_batch.ptrs.data_ptr(), comp_batch.sizes.data_ptr(), out.sizes.data_ptr(), actual.data_ptr(), n,
+                   dtemp.data_ptr(), dtemp.numel(), out.ptrs.data_ptr(), status.data_ptr(),
+                   C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert st == 0
 
-    plan.back.zero_()
-    total = step()
-    assert int(h_status.abs().sum().item()) == 0 and torch.equal(h_back, h_raw), "e2e round trip failed"
+    clocks = ClockSampler(local)
+    clocks.start()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    assert int(status.abs().sum().item()) == 0 and bool((actual == chunk).all().item())
+    assert int(out.buf[: n * chunk].view(torch.int64).sum().item()) == int(check.item()), "C4: decoded bytes differ"
     barrier(world)
     torch.cuda.synchronize()
+    clocks.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(K):
-        total = step()
+    for _ in range(args.steps):
+        step()
     e1.record()
     torch.cuda.synchronize()
+    clocks.mark_end()
     barrier(world)
-    assert int(h_status.abs().sum().item()) == 0 and torch.equal(h_back, h_raw), "e2e round trip failed"
+    clk = clocks.stop()
     t = max_over_ranks(e0.elapsed_time(e1) / 1e3, world, device)
-    tot_bytes = sum_over_ranks(float(nbytes), world, device)
-    return {"value": tot_bytes * K / t / GB, "unit": "GB/s", "h2d_bytes_per_step": nbytes + total + 8 * n,
-            "d2h_bytes_per_step": total + 8 * n + nbytes + 4 * n, "steps": K, "ms_per_step": t / K * 1e3,
-            "slices": S, "streams": len(streams),
-            "path": "pinned host raw -> H2D -> CompressAsync -> gather -> D2H blob+sizes -> H2D -> DecompressAsync -> "
-                    "D2H raw+statuses; slices pipelined over streams, all copies inside the timed region"}
-
-
-def cpu_baseline(args, wl, raw):
-    cpu = CpuCodec(args.codec, wl["chunk"])
-    mib = args.cpu_sample_mib or min(wl["size_mib"], max(64, 32 * cpu.threads))
-    sample = raw[: mib << 20].cpu().numpy()
-    tc, td, cb = cpu.roundtrip_seconds(sample)
-    return {"value": len(sample) / (tc + td) / GB, "unit": "GB/s", "cores": cpu.threads, "kind": cpu.kind,
-            "sample": f"first {mib} MiB of the same workload, {cpu.desc}, {cpu.threads} threads",
-            "compress_GBps": len(sample) / tc / GB, "decompress_GBps": len(sample) / td / GB,
-            "compression_ratio": len(sample) / cb}
+    # the size / status gather of the north star, timed on its own (host wall clock, includes the NCCL all_gathers)
+    tg = None
+    if world > 1:
+        barrier(world)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        g_actual, g_off, first, base = SH.gather_sizes(actual)
+        torch.cuda.synchronize()
+        tg = max_over_ranks(time.perf_counter() - t0, world, device)
+        assert len(g_actual) == nchunks and first == lo and int(g_actual.sum()) == nchunks * chunk
+    my_bytes = float(int(my_sizes.sum().item()))
+    max_share = max_over_ranks(my_bytes, world, device) / max(sum_over_ranks(my_bytes, world, device), 1.0)
+    if rank != 0:
+        return
+    K = args.steps
+    peak, peak_src = load_peaks()
+    total_raw, total_comp = nchunks * chunk, float(np.sum(gsizes))
+    alg = (total_raw + total_comp) / world  # per rank and launch (byte-balanced)
+    line = {
+        "metric": "lz4_decompress_throughput", "value": total_raw * K / t / GB, "unit": "GB/s", "n_gpus": world, "steps": K,
+        "warmup": max(args.warmup, 3), "ms_per_step": t / K * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"C4: LZ4 decompress-only, {nchunks} x {chunk} B chunks ({total_mib} MiB) pre-compressed, "
+                               f"sharded over {world} GPU(s) by sharding.shard_bounds (byte-balanced contiguous ranges)",
+                   "bytes_total": total_raw, "chunk_bytes": chunk, "chunks_total": nchunks,
+                   "largest_rank_share_of_compressed_bytes": max_share,
+                   "l2": "each rank's step reads and writes far more than the 126 MB L2; no explicit flush", "seed": 0xC400},
+        "compression_ratio": total_raw / total_comp,
+        "size_gather_ms": None if tg is None else tg * 1e3,
+        "roofline": {"bound": "hbm", "kernel": "lz4::decompress", "achieved": alg / (t / K) / GB, "peak": peak, "unit": "GB/s",
+                     "frac": alg / (t / K) / GB / peak, **load_traffic("lz4", "decompress", total_raw / world),
+                     "peak_source": peak_src, "ms_per_launch": t / K * 1e3},
+        "gpu_launches": K, "clocks": clk,
+    }
+    print(json.dumps(line), flush=True)
 
 
 # ----------------------------------------------------------------------------- reference arm
 def run_reference(args):
-    """Times the CPU implementation of the same round trip on the host cores (rank 0 only)."""
+    """Times the CPU implementation of the same round trips on the host cores (rank 0 only; the other ranks exit).
+    Each step processes the arm's whole config: bytes_per_gpu x n_gpus, as n_gpus passes over rank 0's buffer."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    wl = dict(WORKLOADS[args.codec])
-    if args.size_mib:
-        wl["size_mib"] = args.size_mib
-    if args.chunk:
-        wl["chunk"] = args.chunk
-    cpu = CpuCodec(args.codec, wl["chunk"])
-    mib = args.cpu_sample_mib or min(wl["size_mib"], max(64, 32 * cpu.threads))
     S = importlib.import_module("hipcomp-core_b200.synth")
     dev = "cuda" if torch.cuda.is_available() else "cpu"
-    gen = {"log_lines": lambda: S.log_lines(mib << 20, wl["seed"], dev),
-           "zipf_text": lambda: S.zipf_text(mib << 20, wl["seed"], dev, chunk=wl["chunk"]),
-           "sorted_ints": lambda: S.sorted_ints((mib << 20) // 4, wl["seed"], dev).view(torch.uint8)}[wl["gen"]]
-    sample = gen().cpu().numpy()
-    W, K = max(args.warmup, 1), args.steps
-    for _ in range(min(W, 2)):
-        cpu.roundtrip_seconds(sample)
-    tcs, tds, cb = [], [], 0
-    for _ in range(K):
-        tc, td, cb = cpu.roundtrip_seconds(sample)
-        tcs.append(tc)
-        tds.append(td)
-    t = sum(tcs) + sum(tds)
-    v = len(sample) * K / t / GB
-    line = {
-        "impl": "reference", "metric": f"{args.codec}_roundtrip_throughput", "value": v, "unit": "GB/s",
-        "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": t / K * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8" if args.codec != "cascaded" else "int32",
-        "data": "synthetic",
-        "config": {"workload": wl["name"], "chunk_bytes": wl["chunk"], "seed": wl["seed"],
-                   "step": f"bounded sample: first {mib} MiB of the workload per step"},
-        "compress_GBps": len(sample) * K / sum(tcs) / GB, "decompress_GBps": len(sample) * K / sum(tds) / GB,
-        "compression_ratio": len(sample) / cb,
-        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": cpu.threads, "kind": cpu.kind,
-                         "sample": f"first {mib} MiB of the same workload, {cpu.desc}, {cpu.threads} threads"},
-        "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
+    codecs = [args.codec] if args.codec else ["lz4", "snappy", "cascaded"]
+    casc_opts = tuple(int(x) for x in args.casc_opts.split(","))
+    ctype, cwidth = CASC_TYPES[args.casc_type]
+    W, K = max(args.warmup, 0), args.steps
+    recs = {}
+    for codec in codecs:
+        wl = workload_for(args, codec)
+        mib = min(args.cpu_sample_mib or wl["size_mib"], wl["size_mib"])
+        gen = {"log_lines": lambda: S.log_lines(mib << 20, wl["seed"], dev),
+               "zipf_text": lambda: S.zipf_text(mib << 20, wl["seed"], dev, chunk=wl["chunk"]),
+               "sorted_ints": lambda: S.sorted_ints((mib << 20) // 4, wl["seed"], dev).view(torch.uint8)}[wl["gen"]]
+        sample = gen().cpu().numpy()
+        cpu = CpuCodec(codec, wl["chunk"], casc=(ctype, *casc_opts, cwidth), threads=args.cpu_threads)
+        for _ in range(min(W, 1)):
+            cpu.roundtrip_seconds(sample)
+        base = cpu.baseline(sample, passes=max(args.gpus, 1), steps=K, with_single=(codec == codecs[0]))
+        nbytes = wl["size_mib"] << 20
+        recs[codec] = {
+            "metric": f"{codec}_roundtrip_throughput", "value": base["value"], "unit": "GB/s",
+            "ms_per_step": base["seconds_per_step"] * 1e3,
+            "dtype": "u8" if codec != "cascaded" else {1: "int8", 2: "int16", 4: "int32", 8: "int64"}[cwidth],
+            "config": make_config(wl, max(args.gpus, 1), nbytes, nbytes // wl["chunk"]),
+            "same_config": mib == wl["size_mib"],
+            "compress_GBps": base["compress_GBps"], "decompress_GBps": base["decompress_GBps"],
+            "compression_ratio": base["compression_ratio"], "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }
+        del sample
+    head = recs[codecs[0]]
+    line = {"impl": "reference", "metric": head["metric"], "value": head["value"], "unit": "GB/s", "n_gpus": args.gpus,
+            "steps": K, "warmup": W, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": head["dtype"], "data": "synthetic",
+            **{k: head[k] for k in ("config", "same_config", "compress_GBps", "decompress_GBps", "compression_ratio",
+                                    "cpu_baseline", "e2e")},
+            "gpu_launches": 0}
+    if len(codecs) > 1:
+        line["codecs"] = {c: recs[c] for c in codecs[1:]}
     print(json.dumps(line), flush=True)
 
 
@@ -647,6 +790,8 @@ if __name__ == "__main__":
     a = parse_args()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "c4":
+        run_c4(a)
     else:
         if a.impl == "refgpu":
             L = importlib.import_module("hipcomp-core_b200._lib")

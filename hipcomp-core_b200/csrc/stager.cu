@@ -93,7 +93,7 @@ struct b200compStager {
   hipcompBatchedLZ4Opts_t lz4_opts;
   hipcompBatchedSnappyOpts_t snappy_opts;
   hipcompBatchedCascadedOpts_t casc_opts;
-  cudaStream_t streams[kStagerStreams] = {};
+  cudaStream_t streams[2 * kStagerStreams] = {}; // [0, 3): compress direction, [3, 6): decompress direction
   std::vector<cudaEvent_t> slice_done, scan_done;
   uint8_t *d_raw = nullptr, *d_back = nullptr, *d_comp = nullptr, *d_blob = nullptr, *d_temp = nullptr, *d_dtemp = nullptr;
   void **d_raw_ptrs = nullptr, **d_back_ptrs = nullptr, **d_comp_ptrs = nullptr, **d_blob_ptrs = nullptr;
@@ -219,7 +219,8 @@ hipcompStatus_t enqueue_decompress_slice(b200compStager* s, int k, const uint8_t
   slice_range(s, nchunks, k, &lo, &hi);
   const size_t n = hi - lo;
   if (!n) return hipcompSuccess;
-  cudaStream_t st = s->streams[k % kStagerStreams];
+  // its own stream set: the H2D copy of a later slice's input must not queue behind this slice's D2H copy
+  cudaStream_t st = s->streams[kStagerStreams + k % kStagerStreams];
   const size_t c0 = s->h_offsets[lo], c1 = s->h_offsets[hi];
   STAGER_CUDA(cudaMemcpyAsync(s->d_blob + c0, h_blob + c0, c1 - c0, cudaMemcpyHostToDevice, st));
   STAGER_CUDA(cudaMemcpyAsync(s->d_blob_sizes + lo, h_sizes + lo, n * sizeof(size_t), cudaMemcpyHostToDevice, st));
@@ -356,7 +357,7 @@ static hipcompStatus_t begin_call(b200compStager* s)
   STAGER_CUDA(cudaMemsetAsync(s->d_running, 0, sizeof(unsigned long long), s->streams[0]));
   cudaEvent_t e = s->scan_done[0];
   STAGER_CUDA(cudaEventRecord(e, s->streams[0]));
-  for (int i = 1; i < kStagerStreams; ++i) STAGER_CUDA(cudaStreamWaitEvent(s->streams[i], e, 0));
+  for (int i = 1; i < 2 * kStagerStreams; ++i) STAGER_CUDA(cudaStreamWaitEvent(s->streams[i], e, 0));
   return hipcompSuccess;
 }
 
