@@ -400,17 +400,27 @@ place_scatter_kernel(const size_t* sizes, size_t* offsets, size_t n, size_t alig
   }
 }
 
+// Chunk g of the container -> (stream pointer, stream size, output pointer, output capacity).  The container is
+// untrusted: a chunk that lies beyond the declared decompressed size, or whose stream does not fit the declared
+// compressed data, is handed to the decoder as an empty stream with no output room and flags the config's status.
 __global__ void __launch_bounds__(256)
-setup_decompress_kernel(const uint8_t* data, const size_t* offsets, uint8_t* decomp, size_t decomp_bytes, size_t chunk,
-                        size_t wave_start, size_t n, const void** comp_ptrs, void** out_ptrs, size_t* out_caps)
+setup_decompress_kernel(const uint8_t* data, const size_t* offsets, const size_t* sizes, const uint64_t* comp_data_size_ptr,
+                        uint8_t* decomp, size_t decomp_bytes, size_t chunk, size_t wave_start, size_t n,
+                        const void** comp_ptrs, size_t* comp_sizes, void** out_ptrs, size_t* out_caps,
+                        hipcompStatus_t* status)
 {
+  const size_t comp_data_size = (size_t)*comp_data_size_ptr; // header word of the (device-resident) container
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const size_t g = wave_start + i;
     const size_t begin = g * chunk;
     const size_t left = begin < decomp_bytes ? decomp_bytes - begin : 0;
-    comp_ptrs[i] = data + offsets[g];
-    out_ptrs[i] = decomp + begin;
-    out_caps[i] = left < chunk ? left : chunk;
+    const size_t off = offsets[g], sz = sizes[g];
+    const bool bad = left == 0 || off > comp_data_size || sz > comp_data_size - off;
+    comp_ptrs[i] = data + (bad ? 0 : off);
+    comp_sizes[i] = bad ? 0 : sz;
+    out_ptrs[i] = decomp + (bad ? 0 : begin);
+    out_caps[i] = bad ? 0 : (left < chunk ? left : chunk);
+    if (bad) *status = hipcompErrorCannotDecompress;
   }
 }
 
@@ -445,13 +455,11 @@ inline T* align8(T* p)
 // format header and the two batched calls.
 namespace {
 
-size_t wave_bytes_target()
-{
-  // uncompressed bytes per wave; the scratch buffer scales with it (B200COMP_HLIF_WAVE_MIB)
-  const char* v = std::getenv("B200COMP_HLIF_WAVE_MIB");
-  const long mib = v ? std::atol(v) : 0;
-  return (size_t)(mib > 0 ? mib : 1024) << 20;
-}
+// Uncompressed bytes per wave: the scratch buffer (compressed-chunk slots) scales with it, while the
+// setup / placement / gather launches around a wave cost ~0.1 ms, so 128 MiB keeps both small.
+constexpr size_t kWaveBytes = (size_t)128 << 20;
+// chunks per decompression wave (36 bytes of scratch each): enough to fill the decoders' grid
+constexpr size_t kDecompWaveChunks = (size_t)1 << 16;
 
 class BatchManager : public hipcompManagerBase
 {
@@ -555,6 +563,13 @@ public:
     cu_check(cudaStreamSynchronize(stream_), "sync");
     cfg.decomp_data_size = header_host_->decomp_data_size;
     cfg.num_chunks = (uint32_t)header_host_->num_chunks;
+    // the container is untrusted: chunk size and chunk count must agree with this manager and with each other
+    const uint64_t want = (header_host_->decomp_data_size + chunk_ - 1) / chunk_;
+    if (header_host_->uncomp_chunk_size != chunk_ || header_host_->num_chunks != want) {
+      *cfg.get_status() = hipcompErrorCannotDecompress;
+      cfg.decomp_data_size = 0;
+      cfg.num_chunks = 0;
+    }
     return cfg;
   }
 
@@ -577,15 +592,17 @@ public:
     const uint8_t* data = reinterpret_cast<const uint8_t*>(sizes + n) + 8 * n;
     scratch_.rewind();
     const void** comp_ptrs = scratch_.reserve<const void*>(dwave_);
+    size_t* comp_sizes = scratch_.reserve<size_t>(dwave_);
     void** out_ptrs = scratch_.reserve<void*>(dwave_);
     size_t* out_caps = scratch_.reserve<size_t>(dwave_);
     size_t* actual = scratch_.reserve<size_t>(dwave_);
     hipcompStatus_t* statuses = scratch_.reserve<hipcompStatus_t>(dwave_);
     for (size_t start = 0; start < n; start += dwave_) {
       const size_t m = n - start < dwave_ ? n - start : dwave_;
-      setup_decompress_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(data, offsets, decomp_buffer, cfg.decomp_data_size,
-                                                                    chunk_, start, m, comp_ptrs, out_ptrs, out_caps);
-      batch_decompress(comp_ptrs, sizes + start, out_caps, actual, m, out_ptrs, statuses);
+      setup_decompress_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(
+          data, offsets, sizes, &reinterpret_cast<const CommonHeader*>(comp_buffer)->comp_data_size, decomp_buffer, cfg.decomp_data_size, chunk_, start, m, comp_ptrs, comp_sizes,
+          out_ptrs, out_caps, cfg.get_status());
+      batch_decompress(comp_ptrs, comp_sizes, out_caps, actual, m, out_ptrs, statuses);
       fold_status_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(statuses, m, cfg.get_status());
     }
     cu_check(cudaGetLastError(), "decompress launches");
@@ -605,15 +622,15 @@ protected:
   void finish_init()
   {
     slot_stride_ = b200comp::round_up_sz(max_comp_chunk(), 16);
-    size_t w = wave_bytes_target() / chunk_;
+    size_t w = kWaveBytes / chunk_;
     if (w < 64) w = 64;
     if (w > (1u << 20)) w = 1u << 20;
     wave_ = w;
-    dwave_ = 1u << 20;
+    dwave_ = kDecompWaveChunks;
     using W = b200comp::Workspace;
     const size_t comp_need = W::footprint<uint8_t>(wave_ * slot_stride_) + W::footprint<uint8_t>(comp_temp_bytes(wave_))
                              + 3 * W::footprint<size_t>(wave_) + 2 * W::footprint<size_t>(wave_ / kPlaceTile + 1);
-    const size_t decomp_need = 4 * W::footprint<size_t>(dwave_) + W::footprint<hipcompStatus_t>(dwave_);
+    const size_t decomp_need = 5 * W::footprint<size_t>(dwave_) + W::footprint<hipcompStatus_t>(dwave_);
     scratch_bytes_ = comp_need > decomp_need ? comp_need : decomp_need;
   }
 

@@ -8,7 +8,8 @@
 // be OWNED by the workspace and obtained from the device's stream-ordered memory pool
 // (cudaMallocAsync / cudaFreeAsync on the caller's stream), so a manager that allocates
 // its scratch on first use never synchronises the device and the memory is recycled by
-// the pool across calls (release threshold raised so the pool keeps it cached).
+// a PRIVATE per-device pool across calls (its release threshold is raised so freed scratch stays
+// cached; the application's default pool is never touched).
 #pragma once
 
 #include <cuda_runtime.h>
@@ -46,9 +47,10 @@ public:
   void acquire(size_t bytes, cudaStream_t stream)
   {
     release();
-    tune_pool_once();
     void* p = nullptr;
-    cudaError_t e = cudaMallocAsync(&p, bytes ? bytes : 1, stream);
+    cudaMemPool_t pool = private_pool();
+    cudaError_t e = pool ? cudaMallocFromPoolAsync(&p, bytes ? bytes : 1, pool, stream)
+                         : cudaMallocAsync(&p, bytes ? bytes : 1, stream);
     if (e != cudaSuccess) {
       cudaGetLastError();
       throw std::runtime_error(std::string("Workspace: cudaMallocAsync(") + std::to_string(bytes)
@@ -111,19 +113,31 @@ public:
   }
 
 private:
-  static void tune_pool_once()
+  // The library's own stream-ordered pool on the current device (created on first use, kept for the life of
+  // the process).  Freed scratch stays cached in it; the host application's default pool keeps its settings.
+  static cudaMemPool_t private_pool()
   {
-    // keep freed scratch cached in the pool instead of returning it to the driver
-    static thread_local int tuned_dev = -1;
+    constexpr int kMaxDevices = 64;
+    static cudaMemPool_t pools[kMaxDevices] = {};
+    static bool tried[kMaxDevices] = {};
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev == tuned_dev) return;
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-      unsigned long long keep = ~0ull;
-      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+    if (!tried[dev]) {
+      tried[dev] = true;
+      cudaMemPoolProps props = {};
+      props.allocType = cudaMemAllocationTypePinned;
+      props.handleTypes = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = dev;
+      cudaMemPool_t pool = nullptr;
+      if (cudaMemPoolCreate(&pool, &props) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        pools[dev] = pool;
+      }
+      cudaGetLastError();
     }
-    cudaGetLastError();
-    tuned_dev = dev;
+    return pools[dev];
   }
 
   uint8_t* base_ = nullptr;
