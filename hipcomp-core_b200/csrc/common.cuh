@@ -49,15 +49,6 @@ inline void allow_smem(K kernel, int bytes)
   cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
-// 4, 8, 16 or 32 from an environment variable (tuning knob), else 0.
-int group_lanes_from_env(const char* name);
-
-// LZ4 / Snappy decoder variant knob (B200COMP_{LZ4,SNAPPY}_DEC_G): unset -> default,
-// (LZ4: "win", the window decoder; Snappy: "round"), "pipe" -> decoupled parse/exec pipeline, "round" -> one-warp
-// round decoder, "win" -> window decoder (shared-memory staged token walk),
-// 4/8/16/32 -> v2 sub-warp group decoder of that width.
-enum : int { kDecoderDefault = -1, kDecoderPipeline = 1, kDecoderRound = 0, kDecoderWindow = 2 };
-int decoder_variant_from_env(const char* name);
 
 inline size_t round_up_sz(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

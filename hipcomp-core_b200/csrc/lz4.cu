@@ -3,7 +3,7 @@
 // C ABI replaces reference src/lowlevel/LZ4Batch.cpp:71-224.
 //
 // Encoders.  Chunks up to 64 KiB (every headline configuration) go to the team encoder of
-// lz4_team.cuh: one CTA per chunk, chunk and hash table resident in shared memory, all
+// lz_team_encode.cuh: one CTA per chunk, chunk and hash table resident in shared memory, all
 // positions matched in parallel.  Its streams are plain LZ4 blocks with a ratio at or above the
 // reference's, but not the reference's bytes.  Larger chunks (up to the format's 16 MiB) keep
 // the one-warp-per-chunk kernel below, which reproduces the reference's greedy policy
@@ -12,9 +12,6 @@
 // The decoder bounds every compressed read (the reference's does not).
 #include "lz_common.cuh"
 #include "lz_team_encode.cuh"
-#include "lz_pipeline.cuh"
-
-#include <cstdlib>
 
 #pragma GCC visibility push(default)
 #include "hipcomp/lz4.h"
@@ -232,73 +229,7 @@ compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const*
 
 constexpr int kDecWarps = 4;
 
-__device__ __forceinline__ bool read_lsic(const uint8_t* comp, uint32_t comp_len, uint32_t& ci, uint32_t& value)
-{
-  uint32_t b = 0xff;
-  while (b == 0xff) {
-    if (ci >= comp_len) return false;
-    b = __ldg(comp + ci);
-    ++ci;
-    value += b;
-  }
-  return true;
-}
-
-// A group of G lanes per chunk (32/G chunks advance per warp instruction); every
-// lane of the group parses the token stream, copies are cooperative within the
-// group.  (reference decompressStream, LZ4Kernels.hiph:971-1097)
-template <int G>
-__global__ void __launch_bounds__(kDecWarps * 32)
-decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
-                  void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
-{
-  constexpr int kGroups = 32 / G;
-  const uint32_t sub = (uint32_t)lane_id() & (G - 1);
-  const unsigned gmask = group_mask<G>();
-  const size_t stride = (size_t)gridDim.x * kDecWarps * kGroups;
-  for (size_t chunk = ((size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5)) * kGroups + ((uint32_t)lane_id() / G);
-       chunk < batch; chunk += stride) {
-    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
-    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
-    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
-    const size_t cap64 = out_caps[chunk];
-    const uint32_t cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
-    uint32_t ci = 0, di = 0;
-    bool ok = true;
-    while (ci < comp_len) {
-      const uint32_t tok = __ldg(comp + ci);
-      ++ci;
-      uint32_t nlit = tok >> 4;
-      if (nlit == 15 && !read_lsic(comp, comp_len, ci, nlit)) { ok = false; break; }
-      if (nlit > cap - di || nlit > comp_len - ci) { ok = false; break; }
-      group_copy_ro<G>(out + di, comp + ci, nlit, sub);
-      ci += nlit;
-      di += nlit;
-      if (ci < comp_len) {
-        if (ci + 2 > comp_len) { ok = false; break; }
-        const uint32_t off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
-        ci += 2;
-        uint32_t mlen = 4 + (tok & 15);
-        if ((tok & 15) == 15 && !read_lsic(comp, comp_len, ci, mlen)) { ok = false; break; }
-        if (off == 0 || off > di || mlen > cap - di) { ok = false; break; }
-        __syncwarp(gmask);
-        group_copy_match<G>(out + di, off, mlen, sub, gmask);
-        di += mlen;
-        __syncwarp(gmask);
-      }
-    }
-    if (sub == 0) {
-      if (actual) actual[chunk] = ok ? di : 0;
-      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
-    }
-    __syncwarp(gmask);
-  }
-}
-
-// v3 decoder: one warp per chunk, rounds of up to 32 sequences (lz_common.cuh,
-// "round executor").  Parsing a round touches only the compressed stream, so the
-// dependent chain per sequence is token -> lengths -> next token; the copies of
-// the whole round then run 32 output bytes per step.
+// length field in 0xFF bytes, read from global memory with a bound on the stream and on the value
 __device__ __forceinline__ bool read_lsic_bounded(const uint8_t* comp, uint32_t comp_len, uint32_t& ci,
                                                   uint32_t& value)
 {
@@ -312,105 +243,7 @@ __device__ __forceinline__ bool read_lsic_bounded(const uint8_t* comp, uint32_t 
   return true;
 }
 
-__global__ void __launch_bounds__(kDecWarps * 32)
-decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
-                        void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
-{
-  const uint32_t lane = (uint32_t)lane_id();
-  const size_t stride = (size_t)gridDim.x * kDecWarps;
-  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
-    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
-    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
-    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
-    const size_t cap64 = out_caps[chunk];
-    const uint32_t cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
-    uint32_t ci = 0, di = 0;
-    bool ok = true;
-    uint32_t win = 0, wpos = 0, wvalid = 0; // register window: stream bytes [wpos, wpos + wvalid)
-    const uintptr_t comp_end_al = (reinterpret_cast<uintptr_t>(comp + comp_len) + 3) & ~(uintptr_t)3;
-    while (ok && ci < comp_len) {
-      // ---- parse up to 32 sequences; lane k keeps sequence k.  Tokens are read from a
-      //      64-byte register window over the stream (lane j holds bytes [2j, 2j+4) of it,
-      //      so one shuffle fetches up to three bytes at any position): no address
-      //      arithmetic and no cache access on the token -> lengths -> next-token chain.
-      uint32_t my_nlit = 0, my_mlen = 0, my_off = 0, my_lp = 0;
-      for (uint32_t k = 0; k < 32 && ci < comp_len; ++k) {
-        if (ci - wpos + 17u > wvalid && wpos + wvalid != comp_len) {
-          const uintptr_t a = reinterpret_cast<uintptr_t>(comp + ci);
-          const uint32_t mis = (uint32_t)(a & 3);
-          const uint32_t* w = reinterpret_cast<const uint32_t*>(a - mis);
-          uint32_t word = 0;
-          if (lane < 18u && reinterpret_cast<uintptr_t>(w + lane) < comp_end_al) word = __ldg(w + lane);
-          const uint32_t o = mis + 2u * lane;
-          const uint32_t lo = __shfl_sync(kFull, word, (int)(o >> 2));
-          const uint32_t hi = __shfl_sync(kFull, word, (int)(o >> 2) + 1);
-          win = __funnelshift_r(lo, hi, (o & 3u) * 8u);
-          wpos = ci;
-          wvalid = min(64u, comp_len - ci);
-        }
-        const uint32_t idx = ci - wpos;
-        uint32_t nlit, mlen = 0, off = 0, lp;
-        bool fast = false;
-        if (idx < wvalid) {
-          const uint32_t tok = (__shfl_sync(kFull, win, (int)(idx >> 1)) >> ((idx & 1u) * 8u)) & 0xffu;
-          nlit = tok >> 4;
-          const uint32_t mc = tok & 15u;
-          const uint32_t oidx = idx + 1u + nlit;
-          if (nlit < 15u && mc < 15u && oidx + 2u <= wvalid) {
-            off = (__shfl_sync(kFull, win, (int)(oidx >> 1)) >> ((oidx & 1u) * 8u)) & 0xffffu;
-            if (off == 0) { ok = false; break; }
-            lp = ci + 1u;
-            mlen = mc + 4u;
-            ci += nlit + 3u;
-            fast = true;
-          }
-        }
-        if (!fast) {
-          const uint32_t tok = __ldg(comp + ci);
-          ++ci;
-          nlit = tok >> 4;
-          if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
-          if (nlit > comp_len - ci) { ok = false; break; }
-          lp = ci;
-          ci += nlit;
-          if (ci < comp_len) {
-            if (ci + 2 > comp_len) { ok = false; break; }
-            off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
-            ci += 2;
-            mlen = 4 + (tok & 15);
-            if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
-            if (off == 0) { ok = false; break; }
-          }
-        }
-        if (lane == k) {
-          my_nlit = nlit;
-          my_mlen = mlen;
-          my_off = off;
-          my_lp = lp;
-        }
-      }
-      if (!ok) break;
-      // ---- place the sequences and validate them
-      uint32_t total;
-      const uint32_t pos = add_sat_u32(di, warp_excl_sum_sat(add_sat_u32(my_nlit, my_mlen), total));
-      const uint32_t lit_end = add_sat_u32(pos, my_nlit);
-      const uint32_t seq_end = add_sat_u32(lit_end, my_mlen);
-      const bool bad = seq_end > cap || (my_mlen != 0 && my_off > lit_end);
-      if (__any_sync(kFull, bad)) { ok = false; break; }
-      const uint32_t end = di + total; // no overflow: every seq_end <= cap
-      execute_round(out, comp, di, end, pos, lit_end, seq_end, my_lp - pos, my_off);
-      di = end;
-    }
-    if (lane == 0) {
-      if (actual) actual[chunk] = ok ? di : 0;
-      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
-    }
-    __syncwarp();
-  }
-}
-
-// v5 decoder ("window" decoder).  The v3 round decoder spends ~65 warp instructions per
-// sequence walking the token chain (every lane repeats the walk).  Here the chain is
+// The decoder: one warp per chunk, rounds of up to 32 sequences.  The serial token chain is
 // reduced to its minimum: a round stages 512 compressed bytes in shared memory (one
 // 16-byte load per lane) and, from the same registers, computes for EVERY byte position
 // the distance to the next token if a token started there (4 positions per SIMD word
@@ -434,11 +267,14 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
   __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin + 32]; // walk may peek <= 18 bytes past the window
   __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
   __shared__ SlowRec s_rec[kDecWarps][32];
+  __shared__ uint32_t s_own[kDecWarps][kOwnWords + 2];       // start bitmap + bases of the round executor
+  __shared__ uint16_t s_idx[kDecWarps][32];                  // token positions found by the fast walk
   const uint32_t lane = (uint32_t)lane_id();
   const int warp = threadIdx.x >> 5;
   uint8_t* win = s_win[warp];
   uint8_t* step = s_step[warp];
   SlowRec* rec = s_rec[warp];
+  uint16_t* idxs = s_idx[warp];
   const size_t stride = (size_t)gridDim.x * kDecWarps;
   for (size_t chunk = (size_t)blockIdx.x * kDecWarps + warp; chunk < batch; chunk += stride) {
     const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
@@ -460,7 +296,6 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       {
         // step[p], for a token at p: 3 + literal nibble (token, literals, offset); bit 7 set when the
         // match nibble is 0xF (a length byte follows the offset); 0 when the literal nibble is 0xF
-        uint4 st;
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
         uint32_t r[4];
 #pragma unroll
@@ -470,20 +305,38 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
           const uint32_t mc15 = ((mc + 0x01010101u) << 3) & 0x80808080u;
           r[j] = ((nl + 0x03030303u) | mc15) & ~(nl15 * 0xffu);
         }
-        st = make_uint4(r[0], r[1], r[2], r[3]);
-        *reinterpret_cast<uint4*>(step + 16 * lane) = st;
+        *reinterpret_cast<uint4*>(step + 16 * lane) = make_uint4(r[0], r[1], r[2], r[3]);
       }
       __syncwarp();
       const bool at_stream_end = wpos + wvalid == comp_len;
 
-      // ---- walk the token chain
+      // ---- walk the token chain.  Fast part: tokens that start at least 19 bytes in front of the window's end
+      // are whole sequences inside the window (a step is at most 18), one table byte each.
       uint32_t idx = shift, k = 0, my_idx = 0;
       bool my_slow = false, giant = false;
+      {
+        const uint32_t wfast = wvalid >= 20u ? wvalid - 19u : 0u;
+#pragma unroll 8
+        for (; k < 32u; ++k) {
+          if (idx >= wfast) break;
+          const uint32_t s = step[idx];
+          uint32_t adv = s & 0x7fu;
+          if (s & 0x80u) {
+            // match length 19..273: exactly one length byte unless it reads 0xFF
+            const uint32_t e = win[idx + adv];
+            adv = e == 0xffu ? 0u : adv + 1u;
+          }
+          if (adv == 0u) break;
+          idxs[k] = (uint16_t)idx;
+          idx += adv;
+        }
+      }
+      const uint32_t kfast = k;
+      // the rest of the round: tokens near the window's end, extended lengths, the last sequence
       while (k < 32u && idx < wvalid) {
         const uint32_t s = step[idx];
         uint32_t adv = s & 0x7fu;
         if (s & 0x80u) {
-          // match length 19..273: exactly one length byte unless it reads 0xFF
           const uint32_t e = win[idx + adv];
           adv = e == 0xffu ? 0u : adv + 1u;
         }
@@ -588,6 +441,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       }
       // ---- lane j decodes sequence j
       __syncwarp();
+      if (lane < kfast) my_idx = idxs[lane];
       uint32_t my_nlit = 0, my_mlen = 0, my_off = 0, my_lp = 0;
       if (lane < k) {
         if (my_slow) {
@@ -614,7 +468,9 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       const bool bad = zero_off || seq_end > cap || (my_mlen != 0 && my_off > lit_end);
       if (__any_sync(kFull, bad)) { ok = false; break; }
       const uint32_t end = di + total;
-      execute_round(out, comp, di, end, pos, lit_end, seq_end, my_lp - pos, my_off);
+      // literal byte p of a sequence is comp[p + (my_lp - pos)], i.e. window byte p + (my_lp - wpos - pos)
+      if (!execute_round_owned(out, win, s_own[warp], di, end, pos, lit_end, seq_end, my_lp - wpos - pos, my_off))
+        execute_round(out, comp, di, end, pos, lit_end, seq_end, my_lp - pos, my_off);
       di = end;
       ci = wpos + idx;
       __syncwarp(); // the window is rewritten next
@@ -625,71 +481,6 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
     }
     __syncwarp();
   }
-}
-
-// Lanes per chunk: narrow groups when the batch has enough chunks to fill the
-// machine with them, the whole warp for small batches.  B200COMP_LZ4_DEC_G overrides.
-// v4 decoder (lz_pipeline.cuh): LZ4 token walk for one parse lane.
-struct PipeCodec {
-  struct State {
-    const uint8_t* comp;
-    uint32_t comp_len, cap, ci, di;
-  };
-  __device__ static void open(State& s, const uint8_t* comp, uint32_t comp_len, size_t cap64)
-  {
-    s.comp = comp;
-    s.comp_len = comp_len;
-    s.cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
-    s.ci = 0;
-    s.di = 0;
-  }
-  __device__ static uint32_t out_pos(const State& s) { return s.di; }
-  __device__ static uint32_t result(const State& s, bool ok) { return ok ? s.di : 0u; }
-  __device__ static int step(State& s, pipe::Desc& d)
-  {
-    uint32_t ci = s.ci;
-    const uint32_t comp_len = s.comp_len;
-    if (ci >= comp_len) return pipe::kDone;
-    const uint8_t* comp = s.comp;
-    const uint32_t tok = __ldg(comp + ci);
-    ++ci;
-    uint32_t nlit = tok >> 4;
-    if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) return pipe::kFail;
-    if (nlit > comp_len - ci || nlit > s.cap - s.di) return pipe::kFail;
-    const uint32_t lp = ci;
-    const uint32_t lit_end = s.di + nlit;
-    ci += nlit;
-    uint32_t mlen = 0, off = 0;
-    if (ci < comp_len) {
-      if (ci + 2 > comp_len) return pipe::kFail;
-      off = (uint32_t)__ldg(comp + ci) | ((uint32_t)__ldg(comp + ci + 1) << 8);
-      ci += 2;
-      mlen = 4 + (tok & 15);
-      if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) return pipe::kFail;
-      if (off == 0 || off > lit_end || mlen > s.cap - lit_end) return pipe::kFail;
-    }
-    d.pos = s.di;
-    d.lit_end = lit_end;
-    d.lp = lp;
-    d.off = off;
-    s.ci = ci;
-    s.di = lit_end + mlen;
-    return pipe::kToken;
-  }
-};
-
-// B200COMP_LZ4_DEC_G = 4/8/16/32 selects the v2 sub-warp-group decoder (kept for
-// comparison and for its tests); the default is the round decoder.
-static int decoder_variant() { return decoder_variant_from_env("B200COMP_LZ4_DEC_G"); }
-
-static int decode_group_lanes(size_t batch)
-{
-  const int forced = group_lanes_from_env("B200COMP_LZ4_DEC_G");
-  if (forced) return forced;
-  const size_t warps = (size_t)sm_count() * 16;
-  if (batch >= warps * 4) return 8;
-  if (batch >= warps * 2) return 16;
-  return 32;
 }
 
 // Size-only walk: one thread per chunk.
@@ -705,7 +496,7 @@ __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_byt
     while (ci < comp_len) {
       const uint32_t tok = comp[ci++];
       uint32_t nlit = tok >> 4;
-      if (nlit == 15 && !read_lsic(comp, comp_len, ci, nlit)) { ok = false; break; }
+      if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
       if (nlit > comp_len - ci) { ok = false; break; }
       ci += nlit;
       di += nlit;
@@ -714,7 +505,7 @@ __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_byt
         const uint32_t off = (uint32_t)comp[ci] | ((uint32_t)comp[ci + 1] << 8);
         ci += 2;
         uint32_t mlen = 4 + (tok & 15);
-        if ((tok & 15) == 15 && !read_lsic(comp, comp_len, ci, mlen)) { ok = false; break; }
+        if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
         if (off == 0 || off > di) { ok = false; break; }
         di += mlen;
       }
@@ -872,12 +663,8 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
   const int smem = global_table ? 0 : (int)(ht * sizeof(uint16_t) * lz4::kCompWarps);
   const size_t need = (batch_size + lz4::kCompWarps - 1) / lz4::kCompWarps;
   // CTAs per SM: with global tables, few enough that every live table stays L2-resident
-  // (B200COMP_LZ4_COMP_CTAS overrides; the workspace always has room: grid * kCompWarps <= batch)
-  static const int env_ctas = [] {
-    const char* v = std::getenv("B200COMP_LZ4_COMP_CTAS");
-    return v ? std::atoi(v) : 0;
-  }();
-  const int ctas_per_sm = env_ctas > 0 ? env_ctas : (global_table ? B200_LZ4_COMP_MINB : 16);
+  // (the workspace always has room: grid * kCompWarps <= batch)
+  const int ctas_per_sm = global_table ? B200_LZ4_COMP_MINB : 16;
   const size_t cap = (size_t)sm_count() * ctas_per_sm;
   const int grid = (int)(need < cap ? need : cap);
   uint16_t* gt = static_cast<uint16_t*>(device_temp_ptr);
@@ -933,47 +720,11 @@ hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compr
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
-  const int variant = lz4::decoder_variant();
-  if (variant == kDecoderPipeline) {
-    const size_t need = (batch_size + pipe::kExecWarps - 1) / pipe::kExecWarps;
-    const size_t cap = (size_t)sm_count() * pipe::kCtasPerSm;
-    pipe::decompress_pipeline_kernel<lz4::PipeCodec><<<(int)(need < cap ? need : cap), pipe::kThreads, 0, stream>>>(
-        device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
-        device_actual_uncompressed_bytes, device_statuses, batch_size);
-    return check_launch(fn);
-  }
-  if (variant == kDecoderDefault || variant == kDecoderWindow) {
-    const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
-    const size_t cap = (size_t)sm_count() * 16;
-    lz4::decompress_window_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
-        device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
-        device_actual_uncompressed_bytes, device_statuses, batch_size);
-    return check_launch(fn);
-  }
-  if (variant == kDecoderRound) {
-    const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
-    const size_t cap = (size_t)sm_count() * 16;
-    lz4::decompress_round_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
-        device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
-        device_actual_uncompressed_bytes, device_statuses, batch_size);
-    return check_launch(fn);
-  }
-  const int g = lz4::decode_group_lanes(batch_size);
-  const size_t per_cta = (size_t)lz4::kDecWarps * (32 / g);
-  const size_t need = (batch_size + per_cta - 1) / per_cta;
+  const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
   const size_t cap = (size_t)sm_count() * 16;
-  const int grid = (int)(need < cap ? need : cap);
-#define B200_LZ4_DEC(G)                                                                                            \
-  lz4::decompress_kernel<G><<<grid, lz4::kDecWarps * 32, 0, stream>>>(                                             \
-      device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,        \
-      device_actual_uncompressed_bytes, device_statuses, batch_size)
-  switch (g) {
-  case 4: B200_LZ4_DEC(4); break;
-  case 8: B200_LZ4_DEC(8); break;
-  case 16: B200_LZ4_DEC(16); break;
-  default: B200_LZ4_DEC(32); break;
-  }
-#undef B200_LZ4_DEC
+  lz4::decompress_window_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
+      device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
+      device_actual_uncompressed_bytes, device_statuses, batch_size);
   return check_launch(fn);
 }
 

@@ -337,4 +337,71 @@ __device__ __forceinline__ void execute_round(uint8_t* out, const uint8_t* comp,
   }
 }
 
+
+// ---- round executor with a start bitmap (the fast path of the window decoders).
+// Conditions: the round produces at most kOwnCap bytes and every match reaches at least 64 bytes back (so a
+// 64-byte step never reads what it writes); all literals of the round lie in the shared-memory window
+// (literal byte p of a sequence is window byte p + win_delta).  own[] (shared memory, 64 words per warp) gets a
+// bitmap of the output bytes where a sequence starts, one word per 32 bytes, and per word the number of
+// starts in front of it: the owner of byte 32 w + l is then base[w] + popc(bits[w] & (2 << l) - 1) - 1, two
+// broadcast loads and three ALU instructions per 32 output bytes.
+// Returns false (nothing written) when the round does not qualify; the caller falls back to execute_round().
+constexpr uint32_t kOwnCap = 1024;      // bytes of output per round on this path
+constexpr uint32_t kOwnWords = 64;      // shared-memory words per warp: 32 bitmap words + 32 bases
+
+__device__ __forceinline__ uint32_t lds_u8_shared(uint32_t sa)
+{
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(sa));
+  return v;
+}
+
+__device__ __forceinline__ bool execute_round_owned(uint8_t* out, const uint8_t* win, uint32_t* own, uint32_t begin,
+                                                    uint32_t end, uint32_t pos, uint32_t lit_end, uint32_t seq_end,
+                                                    uint32_t win_delta, uint32_t off)
+{
+  const uint32_t lane = (uint32_t)lane_id();
+  const uint32_t span = end - begin;
+  const bool far = seq_end == lit_end || off >= 64u;
+  if (span > kOwnCap || !__all_sync(kFull, far)) return false;
+  const unsigned le_mask = 0xFFFFFFFFu >> (31u - lane); // bits 0..lane
+  own[lane] = 0u;
+  __syncwarp();
+  const uint32_t rel = pos - begin;
+  if (seq_end > pos) atomicOr(&own[rel >> 5], 1u << (rel & 31u));
+  __syncwarp();
+  {
+    const uint32_t cnt = (uint32_t)__popc(own[lane]);
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = __shfl_up_sync(kFull, incl, d);
+      if ((int)lane >= d) incl += t;
+    }
+    own[32u + lane] = incl - cnt - 1u; // starts in front of the word, minus one: owner = this + starts up to the byte
+  }
+  __syncwarp();
+  const uint32_t win_sa = (uint32_t)__cvta_generic_to_shared(win) + win_delta; // + p = the literal's window byte
+  for (uint32_t b = 0; b < span; b += 64u) {
+    const uint32_t w = b >> 5;
+    const uint32_t o0 = own[32u + w] + (uint32_t)__popc(own[w] & le_mask);
+    const uint32_t o1 = own[33u + w] + (uint32_t)__popc(own[w + 1u] & le_mask);
+    const uint32_t p0 = begin + b + lane, p1 = p0 + 32u;
+    const bool in0 = p0 < end, in1 = p1 < end;
+    const uint32_t le0 = __shfl_sync(kFull, lit_end, (int)(o0 & 31u)), le1 = __shfl_sync(kFull, lit_end, (int)(o1 & 31u));
+    const uint32_t of0 = __shfl_sync(kFull, off, (int)(o0 & 31u)), of1 = __shfl_sync(kFull, off, (int)(o1 & 31u));
+    const uint32_t wd0 = __shfl_sync(kFull, win_sa, (int)(o0 & 31u)), wd1 = __shfl_sync(kFull, win_sa, (int)(o1 & 31u));
+    const bool lit0 = p0 < le0, lit1 = p1 < le1;
+    uint32_t v0 = 0, v1 = 0;
+    if (in0 && lit0) v0 = lds_u8_shared(wd0 + p0);
+    if (in1 && lit1) v1 = lds_u8_shared(wd1 + p1);
+    if (in0 && !lit0) v0 = out[p0 - of0];
+    if (in1 && !lit1) v1 = out[p1 - of1];
+    if (in0) out[p0] = (uint8_t)v0;
+    if (in1) out[p1] = (uint8_t)v1;
+    __syncwarp();
+  }
+  return true;
+}
+
 } // namespace b200comp

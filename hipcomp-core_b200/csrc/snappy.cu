@@ -9,10 +9,7 @@
 // element grammar of src/snappy/decompression_decode.hiph:72-150 (the reference
 // uses a 3-warp prefetch/decode/process pipeline with nanosleep spin queues).
 #include "lz_common.cuh"
-#include "lz_pipeline.cuh"
 #include "lz_team_encode.cuh"
-
-#include <cstdlib>
 
 #pragma GCC visibility push(default)
 #include "hipcomp/snappy.h"
@@ -193,237 +190,7 @@ __device__ __forceinline__ bool read_preamble(const uint8_t* comp, uint32_t comp
   return true;
 }
 
-// A group of G lanes per chunk, 32/G chunks per warp (see lz_common.cuh).
-template <int G>
-__global__ void __launch_bounds__(kDecWarps * 32)
-decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
-                  void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
-{
-  constexpr int kGroups = 32 / G;
-  const uint32_t sub = (uint32_t)lane_id() & (G - 1);
-  const unsigned gmask = group_mask<G>();
-  const size_t stride = (size_t)gridDim.x * kDecWarps * kGroups;
-  for (size_t chunk = ((size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5)) * kGroups + ((uint32_t)lane_id() / G);
-       chunk < batch; chunk += stride) {
-    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
-    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
-    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
-    const size_t cap64 = out_caps[chunk];
-    uint32_t size = 0, cur = 0, left = 0;
-    bool ok = comp_len != 0 && comp != nullptr;
-    if (ok) ok = read_preamble(comp, comp_len, cur, size);
-    if (ok) {
-      const size_t cap = cap64 == 0 ? size : cap64; // 0 = "trust the preamble" (decompression.hiph:148-149)
-      if ((cur >= comp_len && size != 0) || size > cap) ok = false;
-    }
-    if (!ok) size = 0; // nothing was produced: report 0 bytes
-    if (ok) {
-      left = size;
-      uint32_t dst = 0;
-      while (left > 0) {
-        if (cur >= comp_len) { ok = false; break; }
-        const uint32_t b0 = __ldg(comp + cur);
-        uint32_t blen;
-        if (b0 & 3) {
-          uint32_t offset;
-          if ((b0 & 3) == 1) {
-            if (cur + 2 > comp_len) { ok = false; break; }
-            offset = ((b0 & 0xe0) << 3) | __ldg(comp + cur + 1);
-            blen = ((b0 >> 2) & 7) + 4;
-            cur += 2;
-          } else if ((b0 & 3) == 2) {
-            if (cur + 3 > comp_len) { ok = false; break; }
-            offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8);
-            blen = (b0 >> 2) + 1;
-            cur += 3;
-          } else {
-            if (cur + 5 > comp_len) { ok = false; break; }
-            offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8)
-                     | ((uint32_t)__ldg(comp + cur + 3) << 16) | ((uint32_t)__ldg(comp + cur + 4) << 24);
-            blen = (b0 >> 2) + 1;
-            cur += 5;
-          }
-          if (offset == 0 || offset > dst || left < blen) { ok = false; break; }
-          __syncwarp(gmask);
-          group_copy_match<G>(out + dst, offset, blen, sub, gmask);
-          __syncwarp(gmask);
-        } else {
-          blen = b0 >> 2;
-          cur += 1;
-          if (blen >= 60) {
-            const uint32_t nb = blen - 59;
-            if (cur + nb > comp_len) { ok = false; break; }
-            blen = 0;
-            for (uint32_t i = 0; i < nb; ++i) blen |= (uint32_t)__ldg(comp + cur + i) << (8 * i);
-            cur += nb;
-          }
-          if (blen == 0xffffffffu) { ok = false; break; }
-          blen += 1;
-          if (left < blen || blen > comp_len - cur) { ok = false; break; }
-          group_copy_ro<G>(out + dst, comp + cur, blen, sub);
-          cur += blen;
-        }
-        dst += blen;
-        left -= blen;
-      }
-    }
-    if (sub == 0) {
-      if (actual) actual[chunk] = size - left;
-      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
-    }
-    __syncwarp(gmask);
-  }
-}
-
-// v3 decoder: one warp per chunk, rounds of up to 32 elements (literal or copy),
-// executed by the in-order round executor of lz_common.cuh.  An element that fails
-// validation ends the stream; the elements in front of it are still produced, so
-// the reported progress equals the sequential decoder's (size - bytes_left).
-__global__ void __launch_bounds__(kDecWarps * 32)
-decompress_round_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
-                        void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
-{
-  const uint32_t lane = (uint32_t)lane_id();
-  const size_t stride = (size_t)gridDim.x * kDecWarps;
-  for (size_t chunk = (size_t)blockIdx.x * kDecWarps + (threadIdx.x >> 5); chunk < batch; chunk += stride) {
-    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
-    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
-    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
-    const size_t cap64 = out_caps[chunk];
-    uint32_t size = 0, cur = 0, left = 0;
-    bool ok = comp_len != 0 && comp != nullptr;
-    if (ok) ok = read_preamble(comp, comp_len, cur, size);
-    if (ok) {
-      const size_t cap = cap64 == 0 ? size : cap64;
-      if ((cur >= comp_len && size != 0) || size > cap) ok = false;
-    }
-    if (!ok) size = 0;
-    if (ok) {
-      left = size;
-      uint32_t dst = 0;
-      uint32_t win = 0, wpos = 0, wvalid = 0; // register window: stream bytes [wpos, wpos + wvalid)
-      const uintptr_t comp_end_al = (reinterpret_cast<uintptr_t>(comp + comp_len) + 3) & ~(uintptr_t)3;
-      while (ok && left > 0) {
-        // ---- parse up to 32 elements; lane k keeps element k
-        uint32_t my_len = 0, my_off = 0, my_lp = 0; // my_off == 0: literal
-        uint32_t pdst = dst;                        // output position while parsing
-        for (uint32_t k = 0; k < 32 && left > 0; ++k) {
-          if (cur >= comp_len) { ok = false; break; }
-          // 64-byte register window over the stream (lane j holds bytes [2j, 2j+4)): one
-          // shuffle yields a tag and its two following bytes.
-          if (cur - wpos + 3u > wvalid && wpos + wvalid != comp_len) {
-            const uintptr_t a = reinterpret_cast<uintptr_t>(comp + cur);
-            const uint32_t mis = (uint32_t)(a & 3);
-            const uint32_t* w = reinterpret_cast<const uint32_t*>(a - mis);
-            uint32_t word = 0;
-            if (lane < 18u && reinterpret_cast<uintptr_t>(w + lane) < comp_end_al) word = __ldg(w + lane);
-            const uint32_t o = mis + 2u * lane;
-            const uint32_t lo = __shfl_sync(kFull, word, (int)(o >> 2));
-            const uint32_t hi = __shfl_sync(kFull, word, (int)(o >> 2) + 1);
-            win = __funnelshift_r(lo, hi, (o & 3u) * 8u);
-            wpos = cur;
-            wvalid = min(64u, comp_len - cur);
-          }
-          const uint32_t idx = cur - wpos;
-          uint32_t blen, offset = 0, lp = 0;
-          if (idx + 3u <= wvalid) {
-            const uint32_t t3 = __shfl_sync(kFull, win, (int)(idx >> 1)) >> ((idx & 1u) * 8u);
-            const uint32_t tag = t3 & 0xffu, kind = t3 & 3u;
-            if (kind == 1u || kind == 2u) {
-              if (kind == 1u) {
-                offset = ((tag & 0xe0u) << 3) | ((t3 >> 8) & 0xffu);
-                blen = ((tag >> 2) & 7u) + 4u;
-                cur += 2;
-              } else {
-                offset = (t3 >> 8) & 0xffffu;
-                blen = (tag >> 2) + 1u;
-                cur += 3;
-              }
-              if (offset == 0 || offset > pdst || left < blen) { ok = false; cur = wpos + idx; break; }
-              if (lane == k) {
-                my_len = blen;
-                my_off = offset;
-              }
-              pdst += blen;
-              left -= blen;
-              continue;
-            }
-            if (kind == 0u && tag < (60u << 2)) {
-              blen = (tag >> 2) + 1u;
-              if (left < blen || blen > comp_len - (cur + 1u)) { ok = false; break; }
-              if (lane == k) {
-                my_len = blen;
-                my_off = 0;
-                my_lp = cur + 1u;
-              }
-              cur += 1u + blen;
-              pdst += blen;
-              left -= blen;
-              continue;
-            }
-          }
-          const uint32_t b0 = __ldg(comp + cur);
-          if (b0 & 3) {
-            if ((b0 & 3) == 1) {
-              if (cur + 2 > comp_len) { ok = false; break; }
-              offset = ((b0 & 0xe0) << 3) | __ldg(comp + cur + 1);
-              blen = ((b0 >> 2) & 7) + 4;
-              cur += 2;
-            } else if ((b0 & 3) == 2) {
-              if (cur + 3 > comp_len) { ok = false; break; }
-              offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8);
-              blen = (b0 >> 2) + 1;
-              cur += 3;
-            } else {
-              if (cur + 5 > comp_len) { ok = false; break; }
-              offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8)
-                       | ((uint32_t)__ldg(comp + cur + 3) << 16) | ((uint32_t)__ldg(comp + cur + 4) << 24);
-              blen = (b0 >> 2) + 1;
-              cur += 5;
-            }
-            if (offset == 0 || offset > pdst || left < blen) { ok = false; break; }
-          } else {
-            blen = b0 >> 2;
-            cur += 1;
-            if (blen >= 60) {
-              const uint32_t nb = blen - 59;
-              if (cur + nb > comp_len) { ok = false; break; }
-              blen = 0;
-              for (uint32_t i = 0; i < nb; ++i) blen |= (uint32_t)__ldg(comp + cur + i) << (8 * i);
-              cur += nb;
-            }
-            if (blen == 0xffffffffu) { ok = false; break; }
-            blen += 1;
-            if (left < blen || blen > comp_len - cur) { ok = false; break; }
-            lp = cur;
-            cur += blen;
-          }
-          if (lane == k) {
-            my_len = blen;
-            my_off = offset;
-            my_lp = lp;
-          }
-          pdst += blen;
-          left -= blen;
-        }
-        // ---- run the elements parsed so far (all of them validated)
-        uint32_t total;
-        const uint32_t pos = dst + warp_excl_sum_sat(my_len, total); // total <= size: no saturation
-        const uint32_t seq_end = pos + my_len;
-        const uint32_t lit_end = my_off == 0 ? seq_end : pos;
-        execute_round(out, comp, dst, dst + total, pos, lit_end, seq_end, my_lp - pos, my_off);
-        dst += total;
-      }
-    }
-    if (lane == 0) {
-      if (actual) actual[chunk] = size - left;
-      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
-    }
-    __syncwarp();
-  }
-}
-
-// v5 decoder ("window" decoder, same scheme as lz4::decompress_window_kernel).  A round stages
+// The decoder (same scheme as lz4::decompress_window_kernel): one warp per chunk.  A round stages
 // 512 compressed bytes in shared memory and computes, for every byte position, how far the next
 // element starts if an element started there (tag kinds folded with SIMD-in-word arithmetic), so
 // the serial walk is one shared-memory byte load per element.  Lane k then decodes element k from
@@ -440,6 +207,8 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
 {
   __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin + 32];
   __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
+  __shared__ uint32_t s_own[kDecWarps][kOwnWords + 2];       // start bitmap + bases of the round executor
+  __shared__ uint16_t s_idx[kDecWarps][32];                  // element positions found by the walk
   const uint32_t lane = (uint32_t)lane_id();
   const int warp = threadIdx.x >> 5;
   uint8_t* win = s_win[warp];
@@ -490,14 +259,18 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       __syncwarp();
 
       // ---- walk the element chain
-      uint32_t idx = shift, k = 0, my_idx = 0;
-      while (k < 32u && idx < wvalid) {
+      uint32_t idx = shift, k = 0;
+      uint16_t* idxs = s_idx[warp];
+#pragma unroll 8
+      for (; k < 32u; ++k) {
+        if (idx >= wvalid) break;
         const uint32_t s = step[idx];
         if (s == 0u || idx + s > wvalid) break;
-        if (lane == k) my_idx = idx;
+        idxs[k] = (uint16_t)idx;
         idx += s;
-        ++k;
       }
+      __syncwarp();
+      const uint32_t my_idx = lane < k ? (uint32_t)idxs[lane] : 0u;
       if (k == 0u) {
         // one element straight from global memory: extended literal, or an element cut by the window end
         uint32_t blen, offset = 0;
@@ -580,7 +353,8 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       const uint32_t pos = dst + rel;
       const uint32_t seq_end = pos + my_len;
       const uint32_t lit_end = my_off == 0 ? seq_end : pos;
-      execute_round(out, comp, dst, dst + produced, pos, lit_end, seq_end, my_lp - pos, my_off);
+      if (!execute_round_owned(out, win, s_own[warp], dst, dst + produced, pos, lit_end, seq_end, my_lp - wpos - pos, my_off))
+        execute_round(out, comp, dst, dst + produced, pos, lit_end, seq_end, my_lp - pos, my_off);
       dst += produced;
       left -= produced;
       if (failed) { ok = false; break; }
@@ -595,99 +369,6 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
     }
     __syncwarp();
   }
-}
-
-// v4 decoder (lz_pipeline.cuh): Snappy element walk for one parse lane.
-struct PipeCodec {
-  struct State {
-    const uint8_t* comp;
-    uint32_t comp_len, cur, size, left;
-    bool bad;
-  };
-  __device__ static void open(State& s, const uint8_t* comp, uint32_t comp_len, size_t cap64)
-  {
-    s.comp = comp;
-    s.comp_len = comp_len;
-    s.cur = 0;
-    s.size = 0;
-    bool ok = comp_len != 0 && comp != nullptr;
-    if (ok) ok = read_preamble(comp, comp_len, s.cur, s.size);
-    if (ok) {
-      const size_t cap = cap64 == 0 ? s.size : cap64;
-      if ((s.cur >= comp_len && s.size != 0) || s.size > cap) ok = false;
-    }
-    if (!ok) s.size = 0;
-    s.left = s.size;
-    s.bad = !ok;
-  }
-  __device__ static uint32_t out_pos(const State& s) { return s.size - s.left; }
-  __device__ static uint32_t result(const State& s, bool) { return s.size - s.left; }
-  __device__ static int step(State& s, pipe::Desc& d)
-  {
-    if (s.bad) return pipe::kFail;
-    if (s.left == 0) return pipe::kDone;
-    uint32_t cur = s.cur;
-    const uint32_t comp_len = s.comp_len;
-    if (cur >= comp_len) return pipe::kFail;
-    const uint8_t* comp = s.comp;
-    const uint32_t dst = s.size - s.left;
-    const uint32_t b0 = __ldg(comp + cur);
-    uint32_t blen, offset = 0, lp = 0;
-    if (b0 & 3) {
-      if ((b0 & 3) == 1) {
-        if (cur + 2 > comp_len) return pipe::kFail;
-        offset = ((b0 & 0xe0) << 3) | __ldg(comp + cur + 1);
-        blen = ((b0 >> 2) & 7) + 4;
-        cur += 2;
-      } else if ((b0 & 3) == 2) {
-        if (cur + 3 > comp_len) return pipe::kFail;
-        offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8);
-        blen = (b0 >> 2) + 1;
-        cur += 3;
-      } else {
-        if (cur + 5 > comp_len) return pipe::kFail;
-        offset = (uint32_t)__ldg(comp + cur + 1) | ((uint32_t)__ldg(comp + cur + 2) << 8)
-                 | ((uint32_t)__ldg(comp + cur + 3) << 16) | ((uint32_t)__ldg(comp + cur + 4) << 24);
-        blen = (b0 >> 2) + 1;
-        cur += 5;
-      }
-      if (offset == 0 || offset > dst || s.left < blen) return pipe::kFail;
-    } else {
-      blen = b0 >> 2;
-      cur += 1;
-      if (blen >= 60) {
-        const uint32_t nb = blen - 59;
-        if (cur + nb > comp_len) return pipe::kFail;
-        blen = 0;
-        for (uint32_t i = 0; i < nb; ++i) blen |= (uint32_t)__ldg(comp + cur + i) << (8 * i);
-        cur += nb;
-      }
-      if (blen == 0xffffffffu) return pipe::kFail;
-      blen += 1;
-      if (s.left < blen || blen > comp_len - cur) return pipe::kFail;
-      lp = cur;
-      cur += blen;
-    }
-    d.pos = dst;
-    d.lit_end = offset == 0 ? dst + blen : dst;
-    d.lp = lp;
-    d.off = offset;
-    s.cur = cur;
-    s.left -= blen;
-    return pipe::kToken;
-  }
-};
-
-static int decoder_variant() { return decoder_variant_from_env("B200COMP_SNAPPY_DEC_G"); }
-
-static int decode_group_lanes(size_t batch)
-{
-  const int forced = group_lanes_from_env("B200COMP_SNAPPY_DEC_G");
-  if (forced) return forced;
-  const size_t warps = (size_t)sm_count() * 16;
-  if (batch >= warps * 4) return 8;
-  if (batch >= warps * 2) return 16;
-  return 32;
 }
 
 __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, size_t* sizes, size_t batch)
@@ -846,48 +527,11 @@ hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_co
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
   if (batch_size == 0) return hipcompSuccess;
-  const int variant = snappy::decoder_variant();
-  if (variant == kDecoderPipeline) {
-    const size_t need = (batch_size + pipe::kExecWarps - 1) / pipe::kExecWarps;
-    const size_t cap = (size_t)sm_count() * pipe::kCtasPerSm;
-    pipe::decompress_pipeline_kernel<snappy::PipeCodec>
-        <<<(int)(need < cap ? need : cap), pipe::kThreads, 0, stream>>>(
-            device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
-            device_actual_uncompressed_bytes, device_statuses, batch_size);
-    return check_launch(fn);
-  }
-  if (variant == kDecoderDefault || variant == kDecoderWindow) {
-    const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
-    const size_t cap = (size_t)sm_count() * 16;
-    snappy::decompress_window_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
-        device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
-        device_actual_uncompressed_bytes, device_statuses, batch_size);
-    return check_launch(fn);
-  }
-  if (variant == kDecoderRound) {
-    const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
-    const size_t cap = (size_t)sm_count() * 16;
-    snappy::decompress_round_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
-        device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
-        device_actual_uncompressed_bytes, device_statuses, batch_size);
-    return check_launch(fn);
-  }
-  const int g = snappy::decode_group_lanes(batch_size);
-  const size_t per_cta = (size_t)snappy::kDecWarps * (32 / g);
-  const size_t need = (batch_size + per_cta - 1) / per_cta;
+  const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
   const size_t cap = (size_t)sm_count() * 16;
-  const int grid = (int)(need < cap ? need : cap);
-#define B200_SNAPPY_DEC(G)                                                                                         \
-  snappy::decompress_kernel<G><<<grid, snappy::kDecWarps * 32, 0, stream>>>(                                       \
-      device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,          \
-      device_actual_uncompressed_bytes, device_statuses, batch_size)
-  switch (g) {
-  case 4: B200_SNAPPY_DEC(4); break;
-  case 8: B200_SNAPPY_DEC(8); break;
-  case 16: B200_SNAPPY_DEC(16); break;
-  default: B200_SNAPPY_DEC(32); break;
-  }
-#undef B200_SNAPPY_DEC
+  snappy::decompress_window_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
+      device_compresed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptr,
+      device_actual_uncompressed_bytes, device_statuses, batch_size);
   return check_launch(fn);
 }
 
@@ -929,8 +573,7 @@ hipcompStatus_t hipcompBatchedSnappyCompressAsync(const void* const* device_unco
   constexpr size_t kMapBytes = sizeof(uint16_t) << snappy::kHashBits;
   // waves over the batch: 24 warps per SM as 6 CTAs of 4, or 28 as one CTA
   const size_t waves4 = (batch_size + sms * 24 - 1) / (sms * 24), waves28 = (batch_size + sms * 28 - 1) / (sms * 28);
-  static const int forced = [] { const char* v = std::getenv("B200COMP_SNAPPY_COMP_WARPS"); return v ? std::atoi(v) : 0; }();
-  const bool big = forced ? forced == 28 : waves28 < waves4;
+  const bool big = waves28 < waves4;
   if (big) {
     constexpr int W = 28;
     allow_smem(snappy::compress_kernel<W>, (int)(W * kMapBytes));

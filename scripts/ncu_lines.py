@@ -31,7 +31,7 @@ sass = [r for r in rows[1:] if len(r) == len(h)]
 
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, capture_output=True)
-func = re.search(r"void (?:\w+::)*(\w+)", kname).group(1)
+func = re.search(r"(?:void )?(?:\w+::)*(\w+)\s*[<(]", kname.strip(chr(34))).group(1)
 lines = None
 for f in os.listdir(tmp):
     dis = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
@@ -45,14 +45,20 @@ for f in os.listdir(tmp):
         for ln in s.splitlines():
             m = re.search(r'//## File "([^"]+)", line (\d+)(?: inlined at "([^"]+)", line (\d+))?', ln)
             if m:
-                # -gi prints the inline chain innermost first; keep the outermost frame (the kernel's own line)
-                if m.group(3):
+                # -gi prints the inline chain innermost first; keep the outermost frame (the kernel's own line),
+                # or with NCU_LINES_INNER=1 the innermost one (the helper's line)
+                if os.environ.get("NCU_LINES_INNER"):
+                    if fresh:
+                        cur = (os.path.basename(m.group(1)), int(m.group(2)))
+                    fresh = False
+                elif m.group(3):
                     cur = (os.path.basename(m.group(3)), int(m.group(4)))
                 else:
                     cur = (os.path.basename(m.group(1)), int(m.group(2)))
                 continue
             if re.match(r"\s+/\*[0-9a-f]{4}\*/", ln):
                 seq.append(cur)
+                fresh = True
         if len(seq) == len(sass):
             lines = seq
             break

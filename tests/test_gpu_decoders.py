@@ -1,13 +1,6 @@
-"""-m gpu: the LZ4 / Snappy decoders in every variant: the default one-warp round decoder
-(width 0 below), the decoupled parse/exec pipeline decoder ("pipe") and the sub-warp group decoder at
-4, 8, 16, 32 lanes per chunk.
-
-The width is normally picked from the batch size; B200COMP_{LZ4,SNAPPY}_DEC_G forces it so that every
-template instance sees the same inputs: ragged sizes, periodic data with every period 1..40 (overlapping
-matches shorter / longer than the group), long matches and long literal runs (the 16-byte vector paths),
-liblz4 / stock snappy streams, and corrupt streams (statuses must equal the oracle's)."""
-import os
-
+"""-m gpu: the LZ4 / Snappy decoders on inputs chosen for their copy paths: ragged sizes, periodic data with every
+period 1..40 (overlapping matches shorter / longer than a warp step), long matches and long literal runs (the
+16-byte vector paths), liblz4 / stock snappy streams, and corrupt streams (statuses must equal the oracle's)."""
 import numpy as np
 import pytest
 
@@ -16,18 +9,11 @@ import oracle_lib as o
 
 pytestmark = pytest.mark.gpu
 
-ENV = {"lz4": "B200COMP_LZ4_DEC_G", "snappy": "B200COMP_SNAPPY_DEC_G"}
-
 
 def _g():
     import gpu_common
 
     return gpu_common
-
-
-def _force(codec, width):
-    if width:
-        os.environ[ENV[codec]] = str(width)
 
 
 def periodic_chunks(n):
@@ -46,19 +32,14 @@ def periodic_chunks(n):
     return out
 
 
-@pytest.fixture(params=[0, "pipe", 4, 8, 16, 32])
-def width(request):
-    for v in ENV.values():
-        os.environ.pop(v, None)
-    yield request.param
-    for v in ENV.values():
-        os.environ.pop(v, None)
+@pytest.fixture
+def width():
+    return 0  # one decoder per codec; the name is kept in the assertion messages
 
 
 @pytest.mark.parametrize("codec", ["lz4", "snappy"])
 def test_roundtrip_every_group_width(codec, width):
     g = _g()
-    _force(codec, width)
     for max_chunk, chunks in ((9000, periodic_chunks(9000)), (65536, datagen.mixed_chunks(65536, 13, 5)),
                               (2048, [c[: (37 * i) % 2049] for i, c in enumerate(datagen.mixed_chunks(2048, 67, 8))])):
         comp, dec, status, sizes, actual = g.roundtrip(codec, chunks, max_chunk=max_chunk)
@@ -71,7 +52,6 @@ def test_lz4_stock_and_corrupt_streams_every_group_width(width):
     g = _g()
     from test_oracle_lz4 import stock_compress
 
-    _force("lz4", width)
     chunks = periodic_chunks(5000) + datagen.mixed_chunks(4096, 12, 3)
     comp = [stock_compress(c) for c in chunks]
     out, actual, status = g.decode_raw("lz4", comp, [len(c) for c in chunks])
@@ -108,7 +88,6 @@ def test_snappy_stock_and_corrupt_streams_every_group_width(width):
     g = _g()
     import pyarrow as pa
 
-    _force("snappy", width)
     codec = pa.Codec("snappy")
     chunks = periodic_chunks(5000) + datagen.mixed_chunks(4096, 12, 3)
     comp = [np.frombuffer(codec.compress(c.tobytes()).to_pybytes(), np.uint8) for c in chunks]
