@@ -13,6 +13,7 @@ independent: every rank owns its own buffer ("scaling": "weak"), there is no dat
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference|refgpu] [--codec lz4|snappy|cascaded]
   python bench.py --workload c4 [--gpus N]     C4: LZ4 decompress-only, 4 Mi x 4 KiB chunks, strong scaling
+  python bench.py --workload c5 [--gpus N]     C5: input-class sweep (zeros/random/text/ints) x all codecs, one line each
 """
 import argparse
 import ctypes as C
@@ -44,7 +45,8 @@ def parse_args():
                          "own GPU build (oracle/_ref/libhipcomp_ref.so) through the same ABI, for context")
     ap.add_argument("--codec", default=None, choices=["lz4", "snappy", "cascaded"],
                     help="one codec only (default: LZ4 as the line's value, Snappy and Cascaded as codecs.*)")
-    ap.add_argument("--workload", default="default", choices=["default", "c4"])
+    ap.add_argument("--workload", default="default", choices=["default", "c4", "c5"])
+    ap.add_argument("--c5-gib", type=int, default=16, help="C5: GiB per input class (whole job), cut into waves of <= 4 GiB per GPU")
     ap.add_argument("--size-mib", type=int, default=None, help="uncompressed MiB per GPU (default: the BASELINE config)")
     ap.add_argument("--chunk", type=int, default=None)
     ap.add_argument("--cpu-sample-mib", type=int, default=None, help="bound the CPU arm's buffer (default: the full config)")
@@ -349,7 +351,9 @@ def make_data(args, wl, rank, device):
         return S.log_lines(nbytes, seed, device)
     if wl["gen"] == "zipf_text":
         return S.zipf_text(nbytes, seed, device, chunk=wl["chunk"])
-    return S.sorted_ints(nbytes // 4, seed, device).view(torch.uint8)
+    width = CASC_TYPES[getattr(args, "casc_type", "int")][1]
+    tdt = {1: torch.int8, 2: torch.int16, 4: torch.int32, 8: torch.int64}[width]
+    return S.sorted_ints(nbytes // width, seed, device, dtype=tdt).view(torch.uint8)
 
 
 class Plan:
@@ -704,6 +708,7 @@ def run_c4(args):
     # the size / status gather of the north star, timed on its own (host wall clock, includes the NCCL all_gathers)
     tg = None
     if world > 1:
+        SH.gather_sizes(actual[: min(n, 1024)])  # the first collective pays NCCL's lazy initialisation
         barrier(world)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -736,6 +741,72 @@ def run_c4(args):
         "gpu_launches": K, "clocks": clk,
     }
     print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- C5
+def run_c5(args):
+    """BASELINE.json configs[4]: mixed-entropy sweep - zeros / random / text / int columns through all three codecs.
+    Each class is --c5-gib GiB for the whole job (strong scaling: every rank takes total / N, in waves of <= 4 GiB);
+    one JSON line per (class, codec) with aggregate compress / decompress GB/s, ratio, roofline fractions and, at
+    N = 1, the CPU arm on a 256 MiB sample of the same class."""
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    world, rank, local = dist_setup(args.gpus)
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    peak, peak_src = load_peaks()
+    chunk = args.chunk or 65536
+    per_rank = (args.c5_gib << 30) // world
+    wave = min(per_rank, 4 << 30)
+    nwaves = max(1, per_rank // wave)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    for klass in ("zeros", "random", "text", "ints"):
+        for codec in ("lz4", "snappy", "cascaded"):
+            a = argparse.Namespace(**vars(args))
+            a.data = klass
+            wl = dict(WORKLOADS[codec], size_mib=wave >> 20, chunk=chunk)
+            t_comp = t_dec = 0.0
+            raw_b = comp_b = 0
+            for w in range(nwaves):
+                wl_w = dict(wl, seed=wl["seed"] + 77 * w)
+                raw = make_data(a, wl_w, rank, device)
+                plan = Plan(codec, raw, chunk, (1, 1, 1), 4)
+                plan.compress()
+                plan.decompress()
+                plan.verify()
+                barrier(world)
+                torch.cuda.synchronize()
+                e0, e1, e2 = ev(), ev(), ev()
+                e0.record()
+                for _ in range(args.steps):
+                    plan.compress()
+                e1.record()
+                for _ in range(args.steps):
+                    plan.decompress()
+                e2.record()
+                torch.cuda.synchronize()
+                t_comp += e0.elapsed_time(e1) / 1e3 / args.steps
+                t_dec += e1.elapsed_time(e2) / 1e3 / args.steps
+                raw_b += raw.numel()
+                comp_b += int(plan.comp_sizes.sum().item())
+                cpu_sample = raw[: 256 << 20].cpu().numpy() if (world == 1 and w == 0 and not args.no_cpu) else None
+                del plan, raw
+                torch.cuda.empty_cache()
+            tc, td = max_over_ranks(t_comp, world, device), max_over_ranks(t_dec, world, device)
+            tot_raw, tot_comp = sum_over_ranks(float(raw_b), world, device), sum_over_ranks(float(comp_b), world, device)
+            if rank != 0:
+                continue
+            line = {"metric": f"{codec}_class_sweep", "workload": "C5", "input_class": klass, "codec": codec, "n_gpus": world,
+                    "bytes_total": tot_raw, "chunk_bytes": chunk, "waves_per_gpu": nwaves, "unit": "GB/s",
+                    "compress_GBps": tot_raw / tc / GB, "decompress_GBps": tot_raw / td / GB,
+                    "compression_ratio": tot_raw / tot_comp,
+                    "roofline_compress_frac": (tot_raw + tot_comp) / world / tc / GB / peak,
+                    "roofline_decompress_frac": (tot_raw + tot_comp) / world / td / GB / peak, "peak": peak,
+                    "peak_source": peak_src, "scaling": "strong", "data": "synthetic"}
+            if cpu_sample is not None:
+                cpu = CpuCodec(codec, chunk, casc=(4, 1, 1, 1, 4), threads=args.cpu_threads)
+                b = cpu.baseline(cpu_sample, with_single=False)
+                line["cpu"] = {k: b[k] for k in ("compress_GBps", "decompress_GBps", "compression_ratio", "cores", "kind", "sample")}
+            print(json.dumps(line), flush=True)
 
 
 # ----------------------------------------------------------------------------- reference arm
@@ -792,6 +863,8 @@ if __name__ == "__main__":
         run_reference(a)
     elif a.workload == "c4":
         run_c4(a)
+    elif a.workload == "c5":
+        run_c5(a)
     else:
         if a.impl == "refgpu":
             L = importlib.import_module("hipcomp-core_b200._lib")

@@ -1355,11 +1355,14 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
 template <typename T, bool kTail>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, void* const* out_ptrs,
-                  const size_t* out_caps, size_t* actual, hipcompStatus_t* statuses, size_t batch)
+                  const size_t* out_caps, size_t* actual, hipcompStatus_t* statuses, size_t batch, int known_type,
+                  int known_tail)
 {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  const uint8_t* p0 = static_cast<const uint8_t*>(comp_ptrs[0]);
-  const int type_id = p0 ? p0[3] : -1;
+  // known_type >= 0: the caller (a manager, the staging pipeline) knows the batch's options and launched only
+  // this instantiation; else the C ABI's rule: partition 0's header decides for the batch
+  const uint8_t* p0 = known_type >= 0 ? nullptr : static_cast<const uint8_t*>(comp_ptrs[0]);
+  const int type_id = known_type >= 0 ? known_type : (p0 ? p0[3] : -1);
   int width;
   switch (type_id) {
   case HIPCOMP_TYPE_CHAR: case HIPCOMP_TYPE_UCHAR: width = 1; break;
@@ -1370,7 +1373,8 @@ decompress_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, void* 
   }
   if (width != (int)sizeof(T)) return;
   if (sizeof(T) == 4) {
-    const bool tail_batch = p0[0] >= 2 && p0[1] == 1 && p0[2] != 0; // num_RLEs, num_deltas, use_bp of partition 0
+    // num_RLEs, num_deltas, use_bp of partition 0
+    const bool tail_batch = known_type >= 0 ? known_tail != 0 : (p0[0] >= 2 && p0[1] == 1 && p0[2] != 0);
     if (tail_batch != kTail) return;
   }
   const int warp = threadIdx.x >> 5;
@@ -1433,13 +1437,50 @@ static hipcompStatus_t launch_decompress(const void* const* comp_ptrs, const siz
   const int per_sm = (227 * 1024) / (smem + 1024);
   const int grid = grid_for(batch, per_sm < 16 ? per_sm : 16);
   decompress_kernel<T, false><<<grid, kWarpsPerCta * 32, smem, stream>>>(comp_ptrs, comp_bytes, out_ptrs, out_caps,
-                                                                        actual, statuses, batch);
+                                                                        actual, statuses, batch, -1, 0);
   if (sizeof(T) == 4) {
     allow_smem(decompress_kernel<T, true>, smem);
     decompress_kernel<T, true><<<grid, kWarpsPerCta * 32, smem, stream>>>(comp_ptrs, comp_bytes, out_ptrs, out_caps,
-                                                                         actual, statuses, batch);
+                                                                         actual, statuses, batch, -1, 0);
   }
   return check_launch("hipcompBatchedCascadedDecompressAsync()");
+}
+
+// One launch: the instantiation the options name (callers that know the batch's options: managers, staging).
+template <typename T, bool kTail>
+static hipcompStatus_t launch_decompress_known(const void* const* comp_ptrs, const size_t* comp_bytes,
+                                               void* const* out_ptrs, const size_t* out_caps, size_t* actual,
+                                               hipcompStatus_t* statuses, size_t batch, int type, cudaStream_t stream)
+{
+  constexpr int smem = DecompSmem<T>::BYTES * kWarpsPerCta;
+  allow_smem(decompress_kernel<T, kTail>, smem);
+  const int per_sm = (227 * 1024) / (smem + 1024);
+  const int grid = grid_for(batch, per_sm < 16 ? per_sm : 16);
+  decompress_kernel<T, kTail><<<grid, kWarpsPerCta * 32, smem, stream>>>(comp_ptrs, comp_bytes, out_ptrs, out_caps, actual,
+                                                                        statuses, batch, type, kTail ? 1 : 0);
+  return check_launch("cascaded::decompress_known()");
+}
+
+hipcompStatus_t decompress_known(const hipcompBatchedCascadedOpts_t& o, const void* const* comp_ptrs,
+                                 const size_t* comp_bytes, const size_t* out_caps, size_t* actual, size_t batch,
+                                 void* const* out_ptrs, hipcompStatus_t* statuses, cudaStream_t stream)
+{
+  if (batch == 0) return hipcompSuccess;
+  const int t = (int)o.type;
+  switch (t) {
+  case HIPCOMP_TYPE_CHAR: case HIPCOMP_TYPE_UCHAR:
+    return launch_decompress_known<uint8_t, false>(comp_ptrs, comp_bytes, out_ptrs, out_caps, actual, statuses, batch, t, stream);
+  case HIPCOMP_TYPE_SHORT: case HIPCOMP_TYPE_USHORT:
+    return launch_decompress_known<uint16_t, false>(comp_ptrs, comp_bytes, out_ptrs, out_caps, actual, statuses, batch, t, stream);
+  case HIPCOMP_TYPE_INT: case HIPCOMP_TYPE_UINT:
+    if (o.num_RLEs >= 2 && o.num_deltas == 1 && o.use_bp != 0)
+      return launch_decompress_known<uint32_t, true>(comp_ptrs, comp_bytes, out_ptrs, out_caps, actual, statuses, batch, t, stream);
+    return launch_decompress_known<uint32_t, false>(comp_ptrs, comp_bytes, out_ptrs, out_caps, actual, statuses, batch, t, stream);
+  case HIPCOMP_TYPE_LONGLONG: case HIPCOMP_TYPE_ULONGLONG:
+    return launch_decompress_known<unsigned long long, false>(comp_ptrs, comp_bytes, out_ptrs, out_caps, actual, statuses, batch, t, stream);
+  default:
+    return fail(hipcompErrorInvalidValue, "cascaded::decompress_known()", "unsupported element type");
+  }
 }
 
 } // namespace cascaded

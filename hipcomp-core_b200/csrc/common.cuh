@@ -9,6 +9,9 @@
 #include <string>
 
 #include "hipcomp.h"
+#pragma GCC visibility push(default)
+#include "hipcomp/cascaded.h"
+#pragma GCC visibility pop
 
 namespace b200comp {
 
@@ -179,5 +182,14 @@ __device__ __forceinline__ bool warp_copy_stream(uint8_t* dst, const uint8_t* sr
   if (i < n) dst[i] = __ldg(src + i);
   return true;
 }
+
+namespace cascaded {
+// hipcompBatchedCascadedDecompressAsync for a caller that knows the batch's options (a manager, the staging
+// pipeline): one kernel launch instead of the C ABI's one per element width (which reads partition 0's header
+// on the device, reference CascadedBatch.hip:381-429).
+hipcompStatus_t decompress_known(const hipcompBatchedCascadedOpts_t& o, const void* const* comp_ptrs,
+                                 const size_t* comp_bytes, const size_t* out_caps, size_t* actual, size_t batch,
+                                 void* const* out_ptrs, hipcompStatus_t* statuses, cudaStream_t stream);
+} // namespace cascaded
 
 } // namespace b200comp

@@ -760,8 +760,9 @@ public:
   void batch_decompress(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps, size_t* actual,
                         size_t n, void* const* out_ptrs, hipcompStatus_t* statuses) override
   {
-    st_check(hipcompBatchedCascadedDecompressAsync(comp_ptrs, comp_bytes, out_caps, actual, n, nullptr, 0, out_ptrs,
-                                                   statuses, stream_),
+    // the manager knows the element type and the layers: one launch (the C ABI launches one per width)
+    st_check(b200comp::cascaded::decompress_known(spec_.options, comp_ptrs, comp_bytes, out_caps, actual, n, out_ptrs,
+                                                  statuses, stream_),
              "Cascaded DecompressAsync");
   }
 

@@ -260,14 +260,14 @@ struct SlowRec {
   uint32_t lit_off, nlit, mlen, off;
 };
 
-__global__ void __launch_bounds__(kDecWarps * 32)
+__global__ void __launch_bounds__(kDecWarps * 32, 9)
 decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
                          void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
 {
   __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin + 32]; // walk may peek <= 18 bytes past the window
   __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
   __shared__ SlowRec s_rec[kDecWarps][32];
-  __shared__ uint32_t s_own[kDecWarps][kOwnWords + 2];       // start bitmap + bases of the round executor
+  __shared__ uint32_t s_own[kDecWarps][kOwnWords];           // start bitmap, bases and stage of the round executor
   __shared__ uint16_t s_idx[kDecWarps][32];                  // token positions found by the fast walk
   const uint32_t lane = (uint32_t)lane_id();
   const int warp = threadIdx.x >> 5;

@@ -339,15 +339,19 @@ __device__ __forceinline__ void execute_round(uint8_t* out, const uint8_t* comp,
 
 
 // ---- round executor with a start bitmap (the fast path of the window decoders).
-// Conditions: the round produces at most kOwnCap bytes and every match reaches at least 64 bytes back (so a
-// 64-byte step never reads what it writes); all literals of the round lie in the shared-memory window
-// (literal byte p of a sequence is window byte p + win_delta).  own[] (shared memory, 64 words per warp) gets a
-// bitmap of the output bytes where a sequence starts, one word per 32 bytes, and per word the number of
-// starts in front of it: the owner of byte 32 w + l is then base[w] + popc(bits[w] & (2 << l) - 1) - 1, two
-// broadcast loads and three ALU instructions per 32 output bytes.
+// Condition: the round produces at most kOwnCap bytes; all literals of the round lie in the shared-memory
+// window (literal byte p of a sequence is window byte p + win_delta).
+// own[] (shared memory, kOwnWords words per warp) gets a bitmap of the output bytes where a sequence starts, one
+// word per 32 bytes, and per word the number of starts in front of it: the owner of byte 32 w + l is then
+// base[w] + popc(bits[w] & (2 << l) - 1) - 1, two broadcast loads and three ALU instructions per 32 bytes.
+// A step produces 64 bytes.  A match byte whose source lies inside the match itself (distance shorter than the
+// bytes already produced) is folded back by whole periods to a byte in front of the match; a source that still
+// lies inside the step (a neighbour sequence produced by other lanes of the same step) is taken from a 64-byte
+// stage in shared memory once the lane that produces it has done so - passes until the step is complete, one
+// for steps without such sources.
 // Returns false (nothing written) when the round does not qualify; the caller falls back to execute_round().
 constexpr uint32_t kOwnCap = 1024;      // bytes of output per round on this path
-constexpr uint32_t kOwnWords = 64;      // shared-memory words per warp: 32 bitmap words + 32 bases
+constexpr uint32_t kOwnWords = 64 + 16; // shared-memory words per warp: 32 bitmap words, 32 bases, 64 stage bytes
 
 __device__ __forceinline__ uint32_t lds_u8_shared(uint32_t sa)
 {
@@ -362,8 +366,7 @@ __device__ __forceinline__ bool execute_round_owned(uint8_t* out, const uint8_t*
 {
   const uint32_t lane = (uint32_t)lane_id();
   const uint32_t span = end - begin;
-  const bool far = seq_end == lit_end || off >= 64u;
-  if (span > kOwnCap || !__all_sync(kFull, far)) return false;
+  if (span > kOwnCap) return false;
   const unsigned le_mask = 0xFFFFFFFFu >> (31u - lane); // bits 0..lane
   own[lane] = 0u;
   __syncwarp();
@@ -381,24 +384,88 @@ __device__ __forceinline__ bool execute_round_owned(uint8_t* out, const uint8_t*
     own[32u + lane] = incl - cnt - 1u; // starts in front of the word, minus one: owner = this + starts up to the byte
   }
   __syncwarp();
+  // every match of the round reaches at least 64 bytes back: a 64-byte step never reads what it writes
+  const bool far = seq_end == lit_end || off >= 64u;
+  if (__all_sync(kFull, far)) {
+    const uint32_t win_sa = (uint32_t)__cvta_generic_to_shared(win) + win_delta; // + p = the literal's window byte
+    for (uint32_t b = 0; b < span; b += 64u) {
+      const uint32_t w = b >> 5;
+      const uint32_t o0 = own[32u + w] + (uint32_t)__popc(own[w] & le_mask);
+      const uint32_t o1 = own[33u + w] + (uint32_t)__popc(own[w + 1u] & le_mask);
+      const uint32_t p0 = begin + b + lane, p1 = p0 + 32u;
+      const bool in0 = p0 < end, in1 = p1 < end;
+      const uint32_t le0 = __shfl_sync(kFull, lit_end, (int)(o0 & 31u)), le1 = __shfl_sync(kFull, lit_end, (int)(o1 & 31u));
+      const uint32_t of0 = __shfl_sync(kFull, off, (int)(o0 & 31u)), of1 = __shfl_sync(kFull, off, (int)(o1 & 31u));
+      const uint32_t wd0 = __shfl_sync(kFull, win_sa, (int)(o0 & 31u)), wd1 = __shfl_sync(kFull, win_sa, (int)(o1 & 31u));
+      const bool lit0 = p0 < le0, lit1 = p1 < le1;
+      uint32_t v0 = 0, v1 = 0;
+      if (in0 && lit0) v0 = lds_u8_shared(wd0 + p0);
+      if (in1 && lit1) v1 = lds_u8_shared(wd1 + p1);
+      if (in0 && !lit0) v0 = out[p0 - of0];
+      if (in1 && !lit1) v1 = out[p1 - of1];
+      if (in0) out[p0] = (uint8_t)v0;
+      if (in1) out[p1] = (uint8_t)v1;
+      __syncwarp();
+    }
+    return true;
+  }
+  uint8_t* stage = reinterpret_cast<uint8_t*>(own + 64);
   const uint32_t win_sa = (uint32_t)__cvta_generic_to_shared(win) + win_delta; // + p = the literal's window byte
+  // x / off for x < kOwnCap by multiplication (exact: x * off < 2^32 whenever the quotient is needed, x >= off)
+  const uint32_t magic = off ? 0xFFFFFFFFu / off + 1u : 0u;
   for (uint32_t b = 0; b < span; b += 64u) {
     const uint32_t w = b >> 5;
     const uint32_t o0 = own[32u + w] + (uint32_t)__popc(own[w] & le_mask);
     const uint32_t o1 = own[33u + w] + (uint32_t)__popc(own[w + 1u] & le_mask);
-    const uint32_t p0 = begin + b + lane, p1 = p0 + 32u;
+    const uint32_t b_abs = begin + b;
+    const uint32_t p0 = b_abs + lane, p1 = p0 + 32u;
     const bool in0 = p0 < end, in1 = p1 < end;
     const uint32_t le0 = __shfl_sync(kFull, lit_end, (int)(o0 & 31u)), le1 = __shfl_sync(kFull, lit_end, (int)(o1 & 31u));
     const uint32_t of0 = __shfl_sync(kFull, off, (int)(o0 & 31u)), of1 = __shfl_sync(kFull, off, (int)(o1 & 31u));
     const uint32_t wd0 = __shfl_sync(kFull, win_sa, (int)(o0 & 31u)), wd1 = __shfl_sync(kFull, win_sa, (int)(o1 & 31u));
+    const uint32_t mg0 = __shfl_sync(kFull, magic, (int)(o0 & 31u)), mg1 = __shfl_sync(kFull, magic, (int)(o1 & 31u));
     const bool lit0 = p0 < le0, lit1 = p1 < le1;
+    // source of a match byte: p - off, folded in front of the match when the match overlaps itself
+    const uint32_t x0 = p0 - le0, x1 = p1 - le1;
+    uint32_t s0 = p0 - of0, s1 = p1 - of1;
+    if (!lit0 && x0 >= of0) s0 = le0 - of0 + (x0 - __umulhi(x0, mg0) * of0);
+    if (!lit1 && x1 >= of1) s1 = le1 - of1 + (x1 - __umulhi(x1, mg1) * of1);
+    bool pend0 = in0 && !lit0 && s0 >= b_abs, pend1 = in1 && !lit1 && s1 >= b_abs;
     uint32_t v0 = 0, v1 = 0;
     if (in0 && lit0) v0 = lds_u8_shared(wd0 + p0);
     if (in1 && lit1) v1 = lds_u8_shared(wd1 + p1);
-    if (in0 && !lit0) v0 = out[p0 - of0];
-    if (in1 && !lit1) v1 = out[p1 - of1];
-    if (in0) out[p0] = (uint8_t)v0;
-    if (in1) out[p1] = (uint8_t)v1;
+    if (in0 && !lit0 && !pend0) v0 = out[s0];
+    if (in1 && !lit1 && !pend1) v1 = out[s1];
+    if (in0 && !pend0) out[p0] = (uint8_t)v0;
+    if (in1 && !pend1) out[p1] = (uint8_t)v1;
+    unsigned wait0 = __ballot_sync(kFull, pend0), wait1 = __ballot_sync(kFull, pend1);
+    if (wait0 | wait1) {
+      // sources inside the step: through the stage, in as many passes as the chain of neighbours is long
+      if (!pend0) stage[lane] = (uint8_t)v0;
+      if (!pend1) stage[32u + lane] = (uint8_t)v1;
+      const uint32_t r0 = s0 - b_abs, r1 = s1 - b_abs; // < 64 when pending
+      while (wait0 | wait1) {
+        __syncwarp();
+        const bool go0 = pend0 && !(((r0 < 32u ? wait0 : wait1) >> (r0 & 31u)) & 1u);
+        const bool go1 = pend1 && !(((r1 < 32u ? wait0 : wait1) >> (r1 & 31u)) & 1u);
+        if (go0) v0 = stage[r0];
+        if (go1) v1 = stage[r1];
+        __syncwarp();
+        if (go0) {
+          stage[lane] = (uint8_t)v0;
+          out[p0] = (uint8_t)v0;
+          pend0 = false;
+        }
+        if (go1) {
+          stage[32u + lane] = (uint8_t)v1;
+          out[p1] = (uint8_t)v1;
+          pend1 = false;
+        }
+        const unsigned n0 = __ballot_sync(kFull, pend0), n1 = __ballot_sync(kFull, pend1);
+        if (n0 == wait0 && n1 == wait1) break; // cannot happen for a validated round (a source lies below its byte)
+        wait0 = n0, wait1 = n1;
+      }
+    }
     __syncwarp();
   }
   return true;

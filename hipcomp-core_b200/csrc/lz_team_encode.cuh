@@ -255,7 +255,8 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
         Xin = s_xstate[warp].x;
       }
       {
-        unsigned longm = __ballot_sync(kFull, is_long);
+        // (a verified part that ends at or before the X in front of the segment is dropped without a look)
+        unsigned longm = __ballot_sync(kFull, is_long && v > Xin);
         while (longm) {
           const int ll = __ffs((int)longm) - 1;
           longm &= longm - 1u;
@@ -282,6 +283,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
               v = mq;
               sts_u16(ends_sa + 64u * (nm - 1u), mq);
             }
+            longm &= __ballot_sync(kFull, v > mq); // everything this match covers is dropped
           }
         }
       }

@@ -207,7 +207,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
 {
   __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin + 32];
   __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
-  __shared__ uint32_t s_own[kDecWarps][kOwnWords + 2];       // start bitmap + bases of the round executor
+  __shared__ uint32_t s_own[kDecWarps][kOwnWords];           // start bitmap, bases and stage of the round executor
   __shared__ uint16_t s_idx[kDecWarps][32];                  // element positions found by the walk
   const uint32_t lane = (uint32_t)lane_id();
   const int warp = threadIdx.x >> 5;

@@ -171,8 +171,8 @@ hipcompStatus_t codec_decompress(b200compStager* s, size_t lo, size_t n, int whi
     return hipcompBatchedSnappyDecompressAsync(in, s->d_blob_sizes + lo, s->d_back_sizes + lo, s->d_actual + lo, n, dtemp,
                                                s->dtemp_bytes, out, s->d_status + lo, st);
   default:
-    return hipcompBatchedCascadedDecompressAsync(in, s->d_blob_sizes + lo, s->d_back_sizes + lo, s->d_actual + lo, n, dtemp,
-                                                 s->dtemp_bytes, out, s->d_status + lo, st);
+    return cascaded::decompress_known(s->casc_opts, in, s->d_blob_sizes + lo, s->d_back_sizes + lo, s->d_actual + lo, n, out,
+                                      s->d_status + lo, st);
   }
 }
 

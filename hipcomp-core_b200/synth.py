@@ -128,10 +128,11 @@ def zipf_text(nbytes, seed, device="cuda", chunk=65536, mixed=True):
     return out
 
 
-def sorted_ints(nelems, seed, device="cuda"):
+def sorted_ints(nelems, seed, device="cuda", dtype=torch.int32):
+    """dtype: torch.int8 / int16 / int32 / int64 - the same column, wrapped to the element width."""
     g = torch.Generator(device=device)
     g.manual_seed(seed)
-    out = torch.empty(nelems, dtype=torch.int32, device=device)
+    out = torch.empty(nelems, dtype=dtype, device=device)
     done, carry = 0, 0
     blk = _BLOCK // 4
     while done < nelems:
@@ -141,6 +142,6 @@ def sorted_ints(nelems, seed, device="cuda"):
         steps = torch.where(zero, torch.zeros_like(geo), geo)
         vals = carry + torch.cumsum(steps, 0)
         carry = int(vals[-1].item())
-        out[done : done + n] = vals.to(torch.int32)  # wraps modulo 2^32 past 2^31 (harmless for the codec)
+        out[done : done + n] = vals.to(dtype)  # wraps modulo 2^width (harmless for the codec)
         done += n
     return out
