@@ -557,6 +557,15 @@ struct TeamEmit {
     }
     return o;
   }
+  // the match part of a long match (len > team::kLongMatch), written by the whole warp
+  static __device__ __forceinline__ void put_match_warp(uint8_t* o, uint32_t d, uint32_t len, uint32_t lane)
+  {
+    if (lane == 0) {
+      o[0] = (uint8_t)(d & 0xffu);
+      o[1] = (uint8_t)(d >> 8);
+    }
+    team::put_lsic(o + 2, len - 4u - 15u);
+  }
   // header of the final literals, written by the whole warp; returns its size
   static __device__ __forceinline__ uint32_t put_tail_header(uint8_t* o, uint32_t nlit, uint32_t lane)
   {

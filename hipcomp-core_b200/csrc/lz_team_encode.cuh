@@ -31,6 +31,7 @@
 namespace b200comp {
 namespace team {
 
+constexpr uint32_t kLongMatch = 1024; // a match longer than this is written by the whole warp
 constexpr uint32_t kLaneSteps = 15; // further 4-byte words a lane verifies behind the first 4 bytes of its match
 
 template <int CAP, int HL, int W>
@@ -247,7 +248,7 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
 
       // ---- 4a. X chain: X = the largest match end in front of the segment.  Long matches are settled here, in
       //          lane order: dropped when the verified part ends at or before the X in front of them, else the
-      //          warp compares 128 bytes per step up to the true end.
+      //          warp compares 512 bytes per step up to the true end.
       uint32_t Xin = 0;
       if (s > 0) {
         mbar_wait(x_bar + 2 * warp, x_phase);
@@ -267,15 +268,20 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
             if ((int)lane == ll) dq = db[31u - (uint32_t)__clz((int)bm) + 32u * lane];
             dq = __shfl_sync(kFull, dq, ll);
             uint32_t mq = E;
-            for (uint32_t a0 = vl; a0 < E; a0 += 128u) {
-              const uint32_t a = a0 + 4u * lane;
-              uint32_t x = 1u;
-              if (a < E) x = lds_u32_unaligned(chunk_sa + a) ^ lds_u32_unaligned(chunk_sa + a - dq);
-              const unsigned diff = __ballot_sync(kFull, x != 0u);
+            for (uint32_t a0 = vl; a0 < E; a0 += 512u) { // 16 bytes per lane and step
+              const uint32_t a = a0 + 16u * lane;
+              uint32_t fd = 16u; // first byte of the lane's 16 that differs (or lies at / behind E)
+#pragma unroll
+              for (int k = 3; k >= 0; --k) {
+                const uint32_t ak = a + 4u * (uint32_t)k;
+                uint32_t x = 1u;
+                if (ak < E) x = lds_u32_unaligned(chunk_sa + ak) ^ lds_u32_unaligned(chunk_sa + ak - dq);
+                if (x) fd = 4u * (uint32_t)k + (((uint32_t)__ffs((int)x) - 1u) >> 3);
+              }
+              const unsigned diff = __ballot_sync(kFull, fd < 16u);
               if (diff) {
                 const int fl = __ffs((int)diff) - 1;
-                const uint32_t xx = __shfl_sync(kFull, x, fl);
-                mq = min(a0 + 4u * (uint32_t)fl + (((uint32_t)__ffs((int)xx) - 1u) >> 3), E);
+                mq = min(a0 + 16u * (uint32_t)fl + __shfl_sync(kFull, fd, fl), E);
                 break;
               }
             }
@@ -376,8 +382,8 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
         uint32_t b = em, k = kfirst, pe = Lf;
         bool first = true;
         uint8_t* o = gout + ob + lane_off;
-        uint32_t long_src = 0, long_cnt = 0;
-        uint8_t* long_dst = nullptr;
+        uint32_t long_src = 0, long_cnt = 0, lm_len = 0, lm_d = 0;
+        uint8_t *long_dst = nullptr, *lm_dst = nullptr;
         while (b) {
           const uint32_t bit = (uint32_t)__ffs((int)b) - 1u;
           b &= b - 1u;
@@ -393,7 +399,11 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
             long_src = pe, long_cnt = nlit, long_dst = o;
           }
           o += nlit;
-          o = Emit::put_match(o, dd, e - q);
+          if (e - q > kLongMatch) { // necessarily the lane's last match: written by the whole warp below
+            lm_dst = o, lm_len = e - q, lm_d = dd;
+          } else {
+            o = Emit::put_match(o, dd, e - q);
+          }
           pe = e;
         }
         // long literal runs: the whole warp copies them, one run at a time
@@ -404,6 +414,15 @@ compress_team_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* c
           const uint32_t srcp = __shfl_sync(kFull, long_src, l), cntl = __shfl_sync(kFull, long_cnt, l);
           uint8_t* dst = reinterpret_cast<uint8_t*>(__shfl_sync(kFull, reinterpret_cast<unsigned long long>(long_dst), l));
           copy_s2g(dst, s_chunk32, mis + srcp, cntl);
+        }
+        // long matches (hundreds of length bytes / copy elements): likewise
+        longm = __ballot_sync(kFull, lm_len != 0u);
+        while (longm) {
+          const int l = __ffs((int)longm) - 1;
+          longm &= longm - 1u;
+          const uint32_t len = __shfl_sync(kFull, lm_len, l), d = __shfl_sync(kFull, lm_d, l);
+          uint8_t* dst = reinterpret_cast<uint8_t*>(__shfl_sync(kFull, reinterpret_cast<unsigned long long>(lm_dst), l));
+          Emit::put_match_warp(dst, d, len, lane);
         }
       }
       if (s + 1 == nseg) {

@@ -454,6 +454,18 @@ struct TeamEmit {
     }
     return o;
   }
+  // the copies of a long match (len > team::kLongMatch), written by the whole warp: 64-byte copies, one per lane
+  // and round, then the rest by one lane
+  static __device__ __forceinline__ void put_match_warp(uint8_t* o, uint32_t d, uint32_t len, uint32_t lane)
+  {
+    const uint32_t k = (len - 68u) / 64u + 1u;
+    for (uint32_t i = lane; i < k; i += 32u) {
+      o[3u * i] = (uint8_t)(((64u - 1u) << 2) | 0x2u);
+      o[3u * i + 1u] = (uint8_t)d;
+      o[3u * i + 2u] = (uint8_t)(d >> 8);
+    }
+    if (lane == 0) put_match(o + 3u * k, d, len - 64u * k);
+  }
   static __device__ __forceinline__ uint32_t put_tail_header(uint8_t* o, uint32_t nlit, uint32_t lane)
   {
     if (lane == 0) put_lit_header(o, nlit, 0);
