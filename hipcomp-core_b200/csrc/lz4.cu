@@ -260,7 +260,7 @@ struct SlowRec {
   uint32_t lit_off, nlit, mlen, off;
 };
 
-__global__ void __launch_bounds__(kDecWarps * 32, 9)
+__global__ void __launch_bounds__(kDecWarps * 32)
 decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
                          void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
 {
@@ -291,7 +291,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       const uint32_t wpos = ci - shift; // stream position of window byte 0 (may "underflow" by < 16 at ci = 0)
       const uint32_t wvalid = min((uint32_t)kWin, comp_len - wpos);
       uint4 v = make_uint4(0, 0, 0, 0);
-      if (16u * lane < wvalid) v = __ldg(reinterpret_cast<const uint4*>(cbase + ci - shift) + lane);
+      if (16u * lane < wvalid) v = ld_block16_guarded(cbase, comp_len, cbase + ci - shift + 16u * lane, win + 16 * lane);
       *reinterpret_cast<uint4*>(win + 16 * lane) = v;
       {
         // step[p], for a token at p: 3 + literal nibble (token, literals, offset); bit 7 set when the

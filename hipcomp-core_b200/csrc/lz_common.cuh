@@ -20,6 +20,23 @@ __device__ __forceinline__ uint32_t ld_unaligned32_ro(const uint8_t* p)
   return __funnelshift_r(lo, hi, sh);
 }
 
+// The 16-byte aligned block at `block` of a stream [base, base + len), for the window decoders (they stage whole
+// aligned blocks; the first and the last one of a stream may stick out of the caller's buffer): one vector load
+// when the block lies inside the stream, else byte loads of the bytes that do, through the lane's own 16 bytes
+// of the shared-memory window `slot` (the rest reads as 0).  The edge path is a rolled loop: two lanes per chunk
+// ever take it, and it must not cost the common path registers.
+__device__ __forceinline__ uint4 ld_block16_guarded(uintptr_t base, uint32_t len, uintptr_t block, uint8_t* slot)
+{
+  if (block >= base && block + 16 <= base + len) return __ldg(reinterpret_cast<const uint4*>(block));
+  *reinterpret_cast<uint4*>(slot) = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll 1
+  for (uint32_t i = 0; i < 16u; ++i) {
+    const uintptr_t a = block + i;
+    if (a >= base && a < base + len) slot[i] = __ldg(reinterpret_cast<const uint8_t*>(a));
+  }
+  return *reinterpret_cast<const uint4*>(slot);
+}
+
 // Warp-cooperative copy of n bytes from read-only memory to `dst`.
 // Short runs: one byte per lane.  Long runs: byte prologue up to a 16-byte
 // aligned destination, then 16-byte stores fed by aligned word loads

@@ -237,7 +237,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       const uint32_t wpos = cur - shift;
       const uint32_t wvalid = min((uint32_t)kWin, comp_len - wpos);
       uint4 v = make_uint4(0, 0, 0, 0);
-      if (16u * lane < wvalid) v = __ldg(reinterpret_cast<const uint4*>(cbase + cur - shift) + lane);
+      if (16u * lane < wvalid) v = ld_block16_guarded(cbase, comp_len, cbase + cur - shift + 16u * lane, win + 16 * lane);
       *reinterpret_cast<uint4*>(win + 16 * lane) = v;
       {
         // step[p] for a tag at p: literal of 1..60 bytes -> 1 + length; copy kinds 1/2/3 -> 2/3/5;

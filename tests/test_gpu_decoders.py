@@ -114,3 +114,27 @@ def test_snappy_stock_and_corrupt_streams_every_group_width(width):
         assert status[i] == st, (width, i)
         assert actual[i] == len(exp), (width, i)
         assert host[i].tobytes() == exp.tobytes()
+
+
+@pytest.mark.parametrize("codec", ["lz4", "snappy"])
+def test_streams_flush_against_the_buffer_ends(codec):
+    """Streams that start at byte 1 of an allocation and end on its last byte, at every 16-byte phase: the decoders stage
+    whole aligned blocks and must not read the bytes around the stream (run this file under
+    `PYTORCH_NO_CUDA_MEMORY_CACHING=1 compute-sanitizer --tool memcheck`, summary in profiles/)."""
+    import torch
+
+    g = _g()
+    rng = np.random.default_rng(5)
+    for phase in range(0, 16, 3):
+        raw = datagen.log_lines(3000 + 7 * phase, 40 + phase)
+        comp = (o.lz4_compress(raw) if codec == "lz4" else o.snappy_compress(raw))
+        buf = torch.empty(phase + 1 + len(comp), dtype=torch.uint8, device="cuda")  # its own allocation, exact size
+        buf[: phase + 1] = 0xEE
+        buf[phase + 1:] = torch.from_numpy(np.ascontiguousarray(comp)).cuda()
+        batch = g.B.DeviceBatch(buf, np.array([phase + 1], dtype=np.int64), np.array([len(comp)], dtype=np.int64))
+        out = g.B.DeviceBatch.empty(1, len(raw) + 16)
+        out.sizes = torch.tensor([len(raw)], dtype=torch.int64, device="cuda")
+        actual, status = g.B.decompress(codec, batch, out)
+        torch.cuda.synchronize()
+        assert int(status[0]) == 0 and int(actual[0]) == len(raw)
+        assert out.to_host(actual)[0].tobytes() == raw.tobytes()
