@@ -483,8 +483,14 @@ def run_e2e(codec, plan, raw, args, world, device, comp_bytes):
     st.close()
     for a in (h_raw, h_back, h_blob, h_sizes, h_status):
         a.free()
-    if world == 1:
-        rec["copy_ceiling"] = copy_ceiling(nbytes, device)
+    # what plain pinned-memory copies give with every rank copying at once (the host side is shared by the ranks)
+    barrier(world)
+    cc = copy_ceiling(nbytes, device)
+    rec["copy_ceiling"] = {"h2d_GBps": sum_over_ranks(cc["h2d_GBps"], world, device),
+                           "d2h_GBps": sum_over_ranks(cc["d2h_GBps"], world, device),
+                           "duplex_GBps_each_way": sum_over_ranks(cc["duplex_GBps_each_way"], world, device),
+                           "bytes_per_rank": cc["bytes"], "ranks_copying_at_once": world,
+                           "note": "sum over ranks of each rank's own rate, all ranks copying concurrently"}
     return rec
 
 

@@ -492,7 +492,7 @@ static void launch_team(const void* const* in_ptrs, const size_t* in_bytes, size
   else if (max_chunk <= 16384)
     launch_team_cfg<16384, 13, 8>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 3);
   else
-    launch_team_cfg<65536, 14, 20>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 1);
+    launch_team_cfg<65536, 14, 24>(in_ptrs, in_bytes, batch, out_ptrs, out_bytes, stream, 1);
 }
 
 } // namespace snappy
