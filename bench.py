@@ -772,6 +772,7 @@ def run_c5(args):
             wl = dict(WORKLOADS[codec], size_mib=wave >> 20, chunk=chunk)
             t_comp = t_dec = 0.0
             raw_b = comp_b = 0
+            cpu_sample = None
             for w in range(nwaves):
                 wl_w = dict(wl, seed=wl["seed"] + 77 * w)
                 raw = make_data(a, wl_w, rank, device)
@@ -794,7 +795,8 @@ def run_c5(args):
                 t_dec += e1.elapsed_time(e2) / 1e3 / args.steps
                 raw_b += raw.numel()
                 comp_b += int(plan.comp_sizes.sum().item())
-                cpu_sample = raw[: 256 << 20].cpu().numpy() if (world == 1 and w == 0 and not args.no_cpu) else None
+                if world == 1 and w == 0 and not args.no_cpu:
+                    cpu_sample = raw[: 256 << 20].cpu().numpy()
                 del plan, raw
                 torch.cuda.empty_cache()
             tc, td = max_over_ranks(t_comp, world, device), max_over_ranks(t_dec, world, device)
