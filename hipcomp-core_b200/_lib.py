@@ -50,6 +50,8 @@ for _c, _opts in (("LZ4", LZ4Opts), ("Snappy", SnappyOpts), ("Cascaded", Cascade
 _vpp = C.POINTER(C.c_void_p)
 EXT_PROTOTYPES = {
     "b200compGatherChunksAsync": [_vp, _vp, _vp, _vp, _sz, _vp],
+    "b200compBatchedCascadedSelectOptsAsync": [_vp, _vp, _sz, C.c_int, _vp, _vp],
+    "b200compBatchedCascadedCompressWithOptsAsync": [_vp, _vp, _sz, _vp, _vp, C.c_int, _vp, _vp],
     "b200compHostAlloc": [_sz, _vpp],
     "b200compStagerCreate": [C.c_int, _sz, _sz, _vp, C.c_int, _vpp],
     "b200compStagerCompress": [_vp, _vp, _sz, _vp, _vp, _szp],

@@ -21,6 +21,7 @@
 
 #pragma GCC visibility push(default)
 #include "hipcomp/cascaded.h"
+#include "hipcomp/b200_ext.h"
 #pragma GCC visibility pop
 
 namespace b200comp {
@@ -962,13 +963,16 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
 template <typename T, bool kR2>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, B200_CASC_COMP_MINB)
 compress_kernel(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs, size_t* out_bytes,
-                size_t batch, int type_id, int R, int D, int bp)
+                size_t batch, int type_id, int R, int D, int bp, const uint8_t* opts_pp)
 {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5;
   uint8_t* smem = smem_raw + (size_t)warp * CompSmem<T>::BYTES;
   const size_t stride = (size_t)gridDim.x * kWarpsPerCta;
   for (size_t p = (size_t)blockIdx.x * kWarpsPerCta + warp; p < batch; p += stride) {
+    if (opts_pp) { // options chosen per partition (b200compBatchedCascadedSelectOptsAsync): 4 bytes each
+      R = opts_pp[4 * p], D = opts_pp[4 * p + 1], bp = opts_pp[4 * p + 2];
+    }
     compress_partition<T, kR2>(static_cast<const T*>(in_ptrs[p]), in_bytes[p], static_cast<uint8_t*>(out_ptrs[p]),
                           out_bytes + p, type_id, R, D, bp, smem);
     __syncwarp();
@@ -1398,6 +1402,96 @@ __global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_byt
   }
 }
 
+// ------------------------------------------------------------------ option selector
+// The reference's cascaded.h:93-99 / CHANGELOG.md:113-116 dropped nvCOMP's selector; the format still carries the
+// option set in every partition header, so a per-partition choice decodes everywhere.  One warp samples the first
+// kSelSample elements of a partition and estimates, from six statistics, the packed size of the option sets
+// {raw, bp, delta+bp, rle+bp, rle+delta+bp}; the smallest wins, ties go to the fewer layers.  Pure integer
+// arithmetic: tests/test_gpu_cascaded_select.py restates it in numpy and demands the same choices.
+constexpr int kSelSample = 1024;
+
+__device__ __forceinline__ uint32_t range_bits(unsigned long long span)
+{
+  return span == 0 ? 0u : 64u - (uint32_t)__clzll((long long)span);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128)
+select_kernel(const void* const* in_ptrs, const size_t* in_bytes, size_t batch, uint8_t* opts_pp)
+{
+  using S = typename std::make_signed<T>::type;
+  const int lane = lane_id();
+  const size_t stride = (size_t)gridDim.x * 4;
+  for (size_t p = (size_t)blockIdx.x * 4 + (threadIdx.x >> 5); p < batch; p += stride) {
+    const T* v = static_cast<const T*>(in_ptrs[p]);
+    const size_t n_total = in_bytes[p] / sizeof(T);
+    const int m = (int)(n_total < (size_t)kSelSample ? n_total : (size_t)kSelSample);
+    unsigned long long vmin = ~0ull, vmax = 0;
+    long long dmin = LLONG_MAX, dmax = LLONG_MIN, rmin = LLONG_MAX, rmax = LLONG_MIN; // all deltas / non-zero deltas
+    uint32_t nruns = 0, maxrun = 0; // maxrun: lane-local maximum of the completed runs, reduced below
+    uint32_t open_len = 0;          // length so far of the run that reaches the current position (uniform)
+    for (int i0 = 0; i0 < m; i0 += 32) {
+      const int i = i0 + lane;
+      const bool in = i < m;
+      const T x = in ? v[i] : (T)0;
+      const T prev = (in && i > 0) ? v[i - 1] : x;
+      if (in) {
+        vmin = min(vmin, (unsigned long long)x);
+        vmax = max(vmax, (unsigned long long)x);
+      }
+      const bool start = in && (i == 0 || x != prev);
+      if (in && i > 0) {
+        const long long d = (long long)(S)(T)(x - prev);
+        dmin = min(dmin, d), dmax = max(dmax, d);
+        if (start) rmin = min(rmin, d), rmax = max(rmax, d);
+      }
+      const unsigned sm = __ballot_sync(kFull, start);
+      const int cnt = min(32, m - i0);
+      nruns += (uint32_t)__popc(sm);
+      if (start) {
+        // the run this lane starts ends at the next start of the group (runs that leave the group stay open)
+        const unsigned above = sm & (0xFFFFFFFEu << lane);
+        if (above) maxrun = max(maxrun, (uint32_t)(__ffs((int)above) - 1 - lane));
+        // the first start of the group closes the run that was open
+        if ((sm & ((1u << lane) - 1u)) == 0u) maxrun = max(maxrun, open_len + (uint32_t)lane);
+      }
+      open_len = sm ? (uint32_t)(cnt - (31 - __clz((int)sm))) : open_len + (uint32_t)cnt;
+    }
+    maxrun = max(maxrun, open_len);
+    maxrun = __reduce_max_sync(kFull, maxrun);
+    // 64-bit reductions by shuffle
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      vmin = min(vmin, (unsigned long long)__shfl_xor_sync(kFull, (long long)vmin, o));
+      vmax = max(vmax, (unsigned long long)__shfl_xor_sync(kFull, (long long)vmax, o));
+      dmin = min(dmin, __shfl_xor_sync(kFull, dmin, o));
+      dmax = max(dmax, __shfl_xor_sync(kFull, dmax, o));
+      rmin = min(rmin, __shfl_xor_sync(kFull, rmin, o));
+      rmax = max(rmax, __shfl_xor_sync(kFull, rmax, o));
+    }
+    if (lane == 0) {
+      uint8_t R = 0, D = 0, bp = 0;
+      if (m >= 2) {
+        const unsigned long long W8 = 8ull * sizeof(T);
+        const unsigned long long vb = range_bits(vmax - vmin);
+        const unsigned long long db = range_bits((unsigned long long)(dmax - dmin));
+        const unsigned long long rb = rmin > rmax ? 0ull : range_bits((unsigned long long)(rmax - rmin));
+        const unsigned long long lb = range_bits(maxrun > 0 ? maxrun - 1u : 0u);
+        const unsigned long long mm = (unsigned long long)m, nr = nruns;
+        unsigned long long best = mm * W8; // raw
+        const unsigned long long s_bp = mm * vb + 64, s_d = (mm - 1) * db + W8 + 64, s_r = nr * (vb + lb) + 128,
+                                 s_rd = (nr > 0 ? nr - 1 : 0) * rb + nr * lb + W8 + 128;
+        if (s_bp < best) best = s_bp, R = 0, D = 0, bp = 1;
+        if (s_d < best) best = s_d, R = 0, D = 1, bp = 1;
+        if (s_r < best) best = s_r, R = 1, D = 0, bp = 1;
+        if (s_rd < best) best = s_rd, R = 1, D = 1, bp = 1;
+      }
+      opts_pp[4 * p] = R, opts_pp[4 * p + 1] = D, opts_pp[4 * p + 2] = bp, opts_pp[4 * p + 3] = 0;
+    }
+    __syncwarp();
+  }
+}
+
 // ------------------------------------------------------------------ launch
 
 static int grid_for(size_t batch, int ctas_per_sm)
@@ -1410,19 +1504,19 @@ static int grid_for(size_t batch, int ctas_per_sm)
 template <typename T>
 static hipcompStatus_t launch_compress(const void* const* in_ptrs, const size_t* in_bytes, void* const* out_ptrs,
                                        size_t* out_bytes, size_t batch, hipcompBatchedCascadedOpts_t o,
-                                       cudaStream_t stream)
+                                       cudaStream_t stream, const uint8_t* opts_pp = nullptr)
 {
   constexpr int smem = CompSmem<T>::BYTES * kWarpsPerCta;
   const int per_sm = (227 * 1024) / (smem + 1024);
   const int grid = grid_for(batch, per_sm < 16 ? per_sm : 16);
-  if (sizeof(T) == 4 && o.num_RLEs == 2 && o.num_deltas == 1) {
+  if (sizeof(T) == 4 && o.num_RLEs == 2 && o.num_deltas == 1 && opts_pp == nullptr) {
     allow_smem(compress_kernel<T, true>, smem); // per device, so not cached in a static
     compress_kernel<T, true><<<grid, kWarpsPerCta * 32, smem, stream>>>(
-        in_ptrs, in_bytes, out_ptrs, out_bytes, batch, (int)o.type, o.num_RLEs, o.num_deltas, o.use_bp);
+        in_ptrs, in_bytes, out_ptrs, out_bytes, batch, (int)o.type, o.num_RLEs, o.num_deltas, o.use_bp, nullptr);
   } else {
     allow_smem(compress_kernel<T, false>, smem);
     compress_kernel<T, false><<<grid, kWarpsPerCta * 32, smem, stream>>>(
-        in_ptrs, in_bytes, out_ptrs, out_bytes, batch, (int)o.type, o.num_RLEs, o.num_deltas, o.use_bp);
+        in_ptrs, in_bytes, out_ptrs, out_bytes, batch, (int)o.type, o.num_RLEs, o.num_deltas, o.use_bp, opts_pp);
   }
   return check_launch("hipcompBatchedCascadedCompressAsync()");
 }
@@ -1519,6 +1613,10 @@ hipcompStatus_t hipcompBatchedCascadedCompressAsync(const void* const* device_un
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_bytes, fn);
   if (o.num_RLEs < 0 || o.num_RLEs > 7 || o.num_deltas < 0 || o.num_deltas > 255 || o.use_bp < 0 || o.use_bp > 1)
     return fail(hipcompErrorInvalidValue, fn, "unsupported cascaded options (num_RLEs in [0,7], use_bp in {0,1})");
   int w;
@@ -1559,6 +1657,10 @@ hipcompStatus_t hipcompBatchedCascadedDecompressAsync(const void* const* device_
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_ptrs, fn);
   hipcompStatus_t s;
   s = cascaded::launch_decompress<uint32_t>(device_compressed_ptrs, device_compressed_bytes, device_uncompressed_ptrs, device_uncompressed_bytes, device_actual_uncompressed_bytes, device_statuses, batch_size, stream);
   if (s != hipcompSuccess) return s;
@@ -1584,6 +1686,69 @@ hipcompStatus_t hipcompBatchedCascadedGetDecompressSizeAsync(const void* const* 
   cascaded::size_kernel<<<(int)(need < cap ? need : cap), 256, 0, stream>>>(device_compressed_ptrs, device_compressed_bytes,
                                                                             device_uncompressed_bytes, batch_size);
   return check_launch(fn);
+}
+
+
+/* ---- extension: per-partition option selection (include/hipcomp/b200_ext.h) */
+hipcompStatus_t b200compBatchedCascadedSelectOptsAsync(const void* const* device_uncompressed_ptrs,
+                                                       const size_t* device_uncompressed_bytes, size_t batch_size,
+                                                       hipcompType_t type, uint8_t* device_opts, hipStream_t stream)
+{
+  static const char* fn = "b200compBatchedCascadedSelectOptsAsync()";
+  if (batch_size == 0) return hipcompSuccess;
+  B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_opts, fn);
+  const size_t need = (batch_size + 3) / 4;
+  const size_t cap = (size_t)sm_count() * 16;
+  const int grid = (int)(need < cap ? need : cap);
+  switch (type) {
+  case HIPCOMP_TYPE_CHAR: case HIPCOMP_TYPE_UCHAR:
+    cascaded::select_kernel<uint8_t><<<grid, 128, 0, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes, batch_size, device_opts);
+    break;
+  case HIPCOMP_TYPE_SHORT: case HIPCOMP_TYPE_USHORT:
+    cascaded::select_kernel<uint16_t><<<grid, 128, 0, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes, batch_size, device_opts);
+    break;
+  case HIPCOMP_TYPE_INT: case HIPCOMP_TYPE_UINT:
+    cascaded::select_kernel<uint32_t><<<grid, 128, 0, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes, batch_size, device_opts);
+    break;
+  case HIPCOMP_TYPE_LONGLONG: case HIPCOMP_TYPE_ULONGLONG:
+    cascaded::select_kernel<unsigned long long><<<grid, 128, 0, stream>>>(device_uncompressed_ptrs, device_uncompressed_bytes, batch_size, device_opts);
+    break;
+  default:
+    return fail(hipcompErrorInvalidValue, fn, "unsupported element type");
+  }
+  return check_launch(fn);
+}
+
+hipcompStatus_t b200compBatchedCascadedCompressWithOptsAsync(const void* const* device_uncompressed_ptrs,
+                                                             const size_t* device_uncompressed_bytes, size_t batch_size,
+                                                             void* const* device_compressed_ptrs,
+                                                             size_t* device_compressed_bytes, hipcompType_t type,
+                                                             const uint8_t* device_opts, hipStream_t stream)
+{
+  static const char* fn = "b200compBatchedCascadedCompressWithOptsAsync()";
+  if (batch_size == 0) return hipcompSuccess;
+  B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
+  B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  B200_CHECK_NOT_NULL(device_opts, fn);
+  hipcompBatchedCascadedOpts_t o = hipcompBatchedCascadedDefaultOpts;
+  o.type = type;
+  o.num_RLEs = 1, o.num_deltas = 1, o.use_bp = 1; // overridden per partition by device_opts
+  switch (type) {
+  case HIPCOMP_TYPE_CHAR: case HIPCOMP_TYPE_UCHAR:
+    return cascaded::launch_compress<uint8_t>(device_uncompressed_ptrs, device_uncompressed_bytes, device_compressed_ptrs, device_compressed_bytes, batch_size, o, stream, device_opts);
+  case HIPCOMP_TYPE_SHORT: case HIPCOMP_TYPE_USHORT:
+    return cascaded::launch_compress<uint16_t>(device_uncompressed_ptrs, device_uncompressed_bytes, device_compressed_ptrs, device_compressed_bytes, batch_size, o, stream, device_opts);
+  case HIPCOMP_TYPE_INT: case HIPCOMP_TYPE_UINT:
+    return cascaded::launch_compress<uint32_t>(device_uncompressed_ptrs, device_uncompressed_bytes, device_compressed_ptrs, device_compressed_bytes, batch_size, o, stream, device_opts);
+  case HIPCOMP_TYPE_LONGLONG: case HIPCOMP_TYPE_ULONGLONG:
+    return cascaded::launch_compress<unsigned long long>(device_uncompressed_ptrs, device_uncompressed_bytes, device_compressed_ptrs, device_compressed_bytes, batch_size, o, stream, device_opts);
+  default:
+    return fail(hipcompErrorInvalidValue, fn, "unsupported element type");
+  }
 }
 
 } // extern "C"

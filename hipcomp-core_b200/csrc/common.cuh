@@ -34,6 +34,26 @@ inline hipcompStatus_t fail(hipcompStatus_t code, const char* fn, const std::str
       return ::b200comp::fail(hipcompErrorInvalidValue, fn, "'" #ptr "' must not be null.");       \
   } while (0)
 
+// The pointer arrays of the batched API must be readable by the device (reference: HipUtils::device_pointer,
+// src/HipUtils.hip:91-108, maps every argument and fails with "Memory location is not accessible by the current
+// GPU").  Plain host memory is rejected here instead of faulting in the kernel; pinned / managed host memory passes.
+inline bool device_accessible(const void* p)
+{
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return attr.type != cudaMemoryTypeUnregistered && attr.devicePointer != nullptr;
+}
+
+#define B200_CHECK_DEVICE_PTR(ptr, fn)                                                             \
+  do {                                                                                             \
+    if (!::b200comp::device_accessible(ptr))                                                       \
+      return ::b200comp::fail(hipcompErrorInvalidValue, fn,                                        \
+                              "'" #ptr "': memory location is not accessible by the current GPU."); \
+  } while (0)
+
 inline hipcompStatus_t check_launch(const char* fn)
 {
   const cudaError_t e = cudaGetLastError();

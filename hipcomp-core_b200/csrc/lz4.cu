@@ -648,6 +648,10 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_bytes, fn);
   switch (format_opts.data_type) {
   case HIPCOMP_TYPE_BITS:
   case HIPCOMP_TYPE_CHAR:
@@ -729,6 +733,10 @@ hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compr
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_ptrs, fn);
   const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
   const size_t cap = (size_t)sm_count() * 16;
   lz4::decompress_window_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(

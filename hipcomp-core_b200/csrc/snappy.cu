@@ -539,6 +539,10 @@ hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_co
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
   if (batch_size == 0) return hipcompSuccess;
+  B200_CHECK_DEVICE_PTR(device_compresed_ptrs, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_ptr, fn);
   const size_t need = (batch_size + snappy::kDecWarps - 1) / snappy::kDecWarps;
   const size_t cap = (size_t)sm_count() * 16;
   snappy::decompress_window_kernel<<<(int)(need < cap ? need : cap), snappy::kDecWarps * 32, 0, stream>>>(
@@ -575,6 +579,10 @@ hipcompStatus_t hipcompBatchedSnappyCompressAsync(const void* const* device_unco
   B200_CHECK_NOT_NULL(device_compressed_ptr, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   if (batch_size == 0) return hipcompSuccess;
+  B200_CHECK_DEVICE_PTR(device_uncompressed_ptr, fn);
+  B200_CHECK_DEVICE_PTR(device_uncompressed_bytes, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_ptr, fn);
+  B200_CHECK_DEVICE_PTR(device_compressed_bytes, fn);
   if (max_uncompressed_chunk_bytes != 0 && max_uncompressed_chunk_bytes <= snappy::kTeamMaxChunk) {
     snappy::launch_team(device_uncompressed_ptr, device_uncompressed_bytes, max_uncompressed_chunk_bytes, batch_size,
                         device_compressed_ptr, device_compressed_bytes, stream);

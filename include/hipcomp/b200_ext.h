@@ -8,6 +8,8 @@
 
 #include "hipcomp.h"
 
+#include <stdint.h>
+
 #include <hip/hip_runtime.h>
 
 #ifdef __cplusplus
@@ -25,6 +27,22 @@ hipcompStatus_t b200compGatherChunksAsync(
     size_t batch_size,
     hipStream_t stream);
 
+
+/* ---- Cascaded option selection per partition (the reference dropped nvCOMP's selector,
+ * include/hipcomp/cascaded.h:93-99, CHANGELOG.md:113-116).  SelectOpts samples the first 1024 elements of every
+ * partition and writes 4 bytes per partition {num_RLEs, num_deltas, use_bp, 0}: the option set with the smallest
+ * estimated packed size among raw / bp / delta+bp / rle+bp / rle+delta+bp.  CompressWithOpts compresses every
+ * partition with its own set; the partition header carries it (format unchanged), so
+ * hipcompBatchedCascadedDecompressAsync - and the reference's decoder - decode the result as usual.  Output slots
+ * as for hipcompBatchedCascadedCompressAsync (GetMaxOutputChunkSize bytes each). */
+hipcompStatus_t b200compBatchedCascadedSelectOptsAsync(const void* const* device_uncompressed_ptrs,
+                                                       const size_t* device_uncompressed_bytes, size_t batch_size,
+                                                       hipcompType_t type, uint8_t* device_opts, hipStream_t stream);
+hipcompStatus_t b200compBatchedCascadedCompressWithOptsAsync(const void* const* device_uncompressed_ptrs,
+                                                             const size_t* device_uncompressed_bytes, size_t batch_size,
+                                                             void* const* device_compressed_ptrs,
+                                                             size_t* device_compressed_bytes, hipcompType_t type,
+                                                             const uint8_t* device_opts, hipStream_t stream);
 
 /* ---- Host-buffer staging pipeline (no reference counterpart: reference CHANGELOG.md:97-98 leaves
  * host <-> device staging to the caller).  One call per direction for data that lives in pinned host memory:

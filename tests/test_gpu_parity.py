@@ -272,3 +272,27 @@ def test_roundtrip_property_many_chunks(codec):
     assert np.concatenate(dec).tobytes() == raw.tobytes()
     ratio = len(raw) / sum(len(c) for c in comp)
     assert ratio > 1.5
+
+
+# ------------------------------------------------------------------ boundary
+@pytest.mark.parametrize("codec", ["lz4", "snappy", "cascaded"])
+def test_host_pointer_arrays_are_rejected_not_dereferenced(codec):
+    """The pointer / size arrays must be device-accessible: plain host memory comes back as hipcompErrorInvalidValue
+    (reference HipUtils::device_pointer, src/HipUtils.hip:91-108), it does not fault in the kernel."""
+    import ctypes as C
+
+    g = _g()
+    lib = g.L.lib()
+    name = {"lz4": "LZ4", "snappy": "Snappy", "cascaded": "Cascaded"}[codec]
+    opts = g.L.CascadedOpts(4096, g.L.TYPE_INT, 1, 1, 1) if codec == "cascaded" else g.B.default_opts(codec)
+    host = (C.c_size_t * 8)()
+    dev = torch.zeros(64, dtype=torch.int64, device="cuda")
+    temp = torch.zeros(1024, dtype=torch.uint8, device="cuda")
+    f = getattr(lib, f"hipcompBatched{name}CompressAsync")
+    st = f(C.addressof(host), dev.data_ptr(), 4096, 4, temp.data_ptr(), temp.numel(), dev.data_ptr(), dev.data_ptr(), opts, None)
+    assert st == g.L.ERROR_INVALID_VALUE
+    f = getattr(lib, f"hipcompBatched{name}DecompressAsync")
+    st = f(dev.data_ptr(), C.addressof(host), dev.data_ptr(), dev.data_ptr(), 4, temp.data_ptr(), temp.numel(), dev.data_ptr(),
+           None, None)
+    assert st == g.L.ERROR_INVALID_VALUE
+    torch.cuda.synchronize()
