@@ -711,6 +711,19 @@ def run_c4(args):
     barrier(world)
     clk = clocks.stop()
     t = max_over_ranks(e0.elapsed_time(e1) / 1e3, world, device)
+    # the size query a decompress-only consumer runs first (hipcompBatchedLZ4GetDecompressSizeAsync), on its own
+    qsizes = torch.zeros(n, dtype=torch.int64, device=device)
+    f_size = lib.hipcompBatchedLZ4GetDecompressSizeAsync
+    q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for it in range(4):
+        if it == 1:
+            q0.record()
+        assert f_size(comp_batch.ptrs.data_ptr(), comp_batch.sizes.data_ptr(), qsizes.data_ptr(), n,
+                      C.c_void_p(torch.cuda.current_stream().cuda_stream)) == 0
+    q1.record()
+    torch.cuda.synchronize()
+    assert bool((qsizes == chunk).all().item())
+    tq = max_over_ranks(q0.elapsed_time(q1) / 3e3, world, device)
     # the size / status gather of the north star, timed on its own (host wall clock, includes the NCCL all_gathers)
     tg = None
     if world > 1:
@@ -741,6 +754,7 @@ def run_c4(args):
                    "l2": "each rank's step reads and writes far more than the 126 MB L2; no explicit flush", "seed": 0xC400},
         "compression_ratio": total_raw / total_comp,
         "size_gather_ms": None if tg is None else tg * 1e3,
+        "size_query_ms": tq * 1e3, "size_query_GBps_of_compressed": total_comp / tq / GB,
         "roofline": {"bound": "hbm", "kernel": "lz4::decompress", "achieved": alg / (t / K) / GB, "peak": peak, "unit": "GB/s",
                      "frac": alg / (t / K) / GB / peak, **load_traffic("lz4", "decompress", total_raw / world),
                      "peak_source": peak_src, "ms_per_launch": t / K * 1e3},

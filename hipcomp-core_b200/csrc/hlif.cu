@@ -456,7 +456,9 @@ inline T* align8(T* p)
 namespace {
 
 // Uncompressed bytes per wave: the scratch buffer (compressed-chunk slots) scales with it, while the
-// setup / placement / gather launches around a wave cost ~0.1 ms, so 128 MiB keeps both small.
+// setup / placement / gather launches around a wave cost ~0.1 ms: 128 MiB for the LZ codecs (a wave takes
+// ~1 ms), 512 MiB for Cascaded, whose kernels need ~0.2 ms for that (measured: CascadedManager compress
+// 1881 GB/s with 1 GiB waves, 1424 with 128 MiB).
 constexpr size_t kWaveBytes = (size_t)128 << 20;
 // chunks per decompression wave (36 bytes of scratch each): enough to fill the decoders' grid
 constexpr size_t kDecompWaveChunks = (size_t)1 << 16;
@@ -486,6 +488,7 @@ public:
   virtual const void* format_header() const = 0;
   virtual size_t format_header_bytes() const = 0;
   virtual size_t max_comp_chunk() const = 0;
+  virtual size_t wave_bytes() const { return kWaveBytes; }
   virtual size_t comp_temp_bytes(size_t n) const = 0;
   virtual size_t chunk_align() const { return 1; }
   virtual void batch_compress(const void* const* in_ptrs, const size_t* in_bytes, size_t n, void* temp, size_t temp_bytes,
@@ -622,7 +625,7 @@ protected:
   void finish_init()
   {
     slot_stride_ = b200comp::round_up_sz(max_comp_chunk(), 16);
-    size_t w = kWaveBytes / chunk_;
+    size_t w = wave_bytes() / chunk_;
     if (w < 64) w = 64;
     if (w > (1u << 20)) w = 1u << 20;
     wave_ = w;
@@ -748,6 +751,7 @@ public:
   const void* format_header() const override { return &spec_; }
   size_t format_header_bytes() const override { return sizeof(CascadedFormatSpecHeader); }
   size_t max_comp_chunk() const override { return max_comp_; }
+  size_t wave_bytes() const override { return (size_t)512 << 20; }
   size_t comp_temp_bytes(size_t) const override { return 0; }
   size_t chunk_align() const override { return 8; } // partitions are read as words of the element type
   void batch_compress(const void* const* in_ptrs, const size_t* in_bytes, size_t n, void* temp, size_t temp_bytes,

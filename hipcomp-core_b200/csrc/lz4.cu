@@ -260,6 +260,9 @@ struct SlowRec {
   uint32_t lit_off, nlit, mlen, off;
 };
 
+// kSizeOnly: the same walk without the output (hipcompBatchedLZ4GetDecompressSizeAsync): `actual` receives the
+// decompressed size of every chunk, 0 for a stream that does not parse.
+template <bool kSizeOnly>
 __global__ void __launch_bounds__(kDecWarps * 32)
 decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
                          void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
@@ -278,9 +281,9 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
   const size_t stride = (size_t)gridDim.x * kDecWarps;
   for (size_t chunk = (size_t)blockIdx.x * kDecWarps + warp; chunk < batch; chunk += stride) {
     const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
-    uint8_t* out = static_cast<uint8_t*>(out_ptrs[chunk]);
+    uint8_t* out = kSizeOnly ? nullptr : static_cast<uint8_t*>(out_ptrs[chunk]);
     const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
-    const size_t cap64 = out_caps[chunk];
+    const size_t cap64 = kSizeOnly ? 0xFFFFFFFEull : out_caps[chunk]; // size query: anything below 4 GiB
     const uint32_t cap = cap64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cap64;
     const uintptr_t cbase = reinterpret_cast<uintptr_t>(comp);
     uint32_t ci = 0, di = 0;
@@ -417,7 +420,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
         uint32_t nlit = tok >> 4;
         if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
         if (nlit > comp_len - ci || nlit > cap - di) { ok = false; break; }
-        group_copy_ro<32>(out + di, comp + ci, nlit, lane);
+        if (!kSizeOnly) group_copy_ro<32>(out + di, comp + ci, nlit, lane);
         ci += nlit;
         di += nlit;
         if (ci < comp_len) {
@@ -428,7 +431,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
           if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
           if (off == 0 || off > di || mlen > cap - di) { ok = false; break; }
           __syncwarp();
-          group_copy_match<32>(out + di, off, mlen, lane, kFull);
+          if (!kSizeOnly) group_copy_match<32>(out + di, off, mlen, lane, kFull);
           di += mlen;
         }
         __syncwarp();
@@ -469,49 +472,19 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       if (__any_sync(kFull, bad)) { ok = false; break; }
       const uint32_t end = di + total;
       // literal byte p of a sequence is comp[p + (my_lp - pos)], i.e. window byte p + (my_lp - wpos - pos)
-      if (!execute_round_owned(out, win, s_own[warp], di, end, pos, lit_end, seq_end, my_lp - wpos - pos, my_off))
-        execute_round(out, comp, di, end, pos, lit_end, seq_end, my_lp - pos, my_off);
+      if (!kSizeOnly) {
+        if (!execute_round_owned(out, win, s_own[warp], di, end, pos, lit_end, seq_end, my_lp - wpos - pos, my_off))
+          execute_round(out, comp, di, end, pos, lit_end, seq_end, my_lp - pos, my_off);
+      }
       di = end;
       ci = wpos + idx;
       __syncwarp(); // the window is rewritten next
     }
     if (lane == 0) {
       if (actual) actual[chunk] = ok ? di : 0;
-      if (statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
+      if (!kSizeOnly && statuses) statuses[chunk] = ok ? hipcompSuccess : hipcompErrorCannotDecompress;
     }
     __syncwarp();
-  }
-}
-
-// Size-only walk: one thread per chunk.
-__global__ void size_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, size_t* sizes, size_t batch)
-{
-  for (size_t chunk = (size_t)blockIdx.x * blockDim.x + threadIdx.x; chunk < batch;
-       chunk += (size_t)gridDim.x * blockDim.x) {
-    const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
-    const uint32_t comp_len = (uint32_t)comp_bytes[chunk];
-    uint32_t ci = 0;
-    unsigned long long di = 0;
-    bool ok = true;
-    while (ci < comp_len) {
-      const uint32_t tok = comp[ci++];
-      uint32_t nlit = tok >> 4;
-      if (nlit == 15 && !read_lsic_bounded(comp, comp_len, ci, nlit)) { ok = false; break; }
-      if (nlit > comp_len - ci) { ok = false; break; }
-      ci += nlit;
-      di += nlit;
-      if (ci < comp_len) {
-        if (ci + 2 > comp_len) { ok = false; break; }
-        const uint32_t off = (uint32_t)comp[ci] | ((uint32_t)comp[ci + 1] << 8);
-        ci += 2;
-        uint32_t mlen = 4 + (tok & 15);
-        if ((tok & 15) == 15 && !read_lsic_bounded(comp, comp_len, ci, mlen)) { ok = false; break; }
-        if (off == 0 || off > di) { ok = false; break; }
-        di += mlen;
-      }
-      if (di > 0xFFFFFFFFull) { ok = false; break; }
-    }
-    sizes[chunk] = ok ? (size_t)di : 0;
   }
 }
 
@@ -739,7 +712,7 @@ hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compr
   B200_CHECK_DEVICE_PTR(device_uncompressed_ptrs, fn);
   const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
   const size_t cap = (size_t)sm_count() * 16;
-  lz4::decompress_window_kernel<<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
+  lz4::decompress_window_kernel<false><<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
       device_compressed_ptrs, device_compressed_bytes, device_uncompressed_bytes, device_uncompressed_ptrs,
       device_actual_uncompressed_bytes, device_statuses, batch_size);
   return check_launch(fn);
@@ -755,10 +728,12 @@ hipcompStatus_t hipcompBatchedLZ4GetDecompressSizeAsync(const void* const* devic
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   if (batch_size == 0) return hipcompSuccess;
-  const size_t need = (batch_size + 127) / 128;
+  // one warp per chunk walks the token chain through the decoder's staged window (a thread per chunk diverges
+  // on every byte: C4 has 4 Mi chunks)
+  const size_t need = (batch_size + lz4::kDecWarps - 1) / lz4::kDecWarps;
   const size_t cap = (size_t)sm_count() * 16;
-  lz4::size_kernel<<<(int)(need < cap ? need : cap), 128, 0, stream>>>(device_compressed_ptrs, device_compressed_bytes,
-                                                                       device_uncompressed_bytes, batch_size);
+  lz4::decompress_window_kernel<true><<<(int)(need < cap ? need : cap), lz4::kDecWarps * 32, 0, stream>>>(
+      device_compressed_ptrs, device_compressed_bytes, nullptr, nullptr, device_uncompressed_bytes, nullptr, batch_size);
   return check_launch(fn);
 }
 
