@@ -131,11 +131,11 @@ def test_roundtrip_sizes(kind, nbytes):
 
 
 @pytest.mark.parametrize("kind", ["lz4", "snappy", "cascaded"])
-def test_multi_wave(kind, monkeypatch):
-    """A 1 MiB wave over 5.3 MiB of input: 6 waves, offsets continue across waves."""
-    monkeypatch.setenv("B200COMP_HLIF_WAVE_MIB", "1")
-    chunk = 4096 if kind == "cascaded" else 16384
-    hdr = run_roundtrip(kind, chunk, 5 * (1 << 20) + 300_000, check_oracle=False)
+def test_multi_wave(kind):
+    """Three waves (the managers cut a buffer into waves of 128 MiB, Cascaded 512 MiB): offsets continue across waves."""
+    chunk = 4096 if kind == "cascaded" else 65536
+    nbytes = (1100 << 20) + 4096 * 3 + 8 if kind == "cascaded" else (300 << 20) + 300_000
+    hdr = run_roundtrip(kind, chunk, nbytes, check_oracle=False)
     offs, sizes = hdr["offsets"].astype(np.int64), hdr["sizes"].astype(np.int64)
     assert offs[0] == 0 and (np.diff(offs) >= sizes[:-1]).all()
     if kind != "cascaded":
@@ -152,8 +152,7 @@ def test_cascaded_default_options():
     run_roundtrip("cascaded", 4096, 4096 * 37 + 64, opts=opts)
 
 
-def test_user_scratch_buffer(monkeypatch):
-    monkeypatch.setenv("B200COMP_HLIF_WAVE_MIB", "8")
+def test_user_scratch_buffer():
     mgr = M.LZ4Manager(16384, L.TYPE_CHAR)
     need = mgr.get_required_scratch_buffer_size()
     assert need > 0
