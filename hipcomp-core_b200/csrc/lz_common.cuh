@@ -1,4 +1,5 @@
-// b200comp — warp-level byte movers shared by the LZ4 and Snappy kernels.
+// b200comp — what the LZ4 and Snappy kernels share: warp-level byte movers, the generic round
+// executor (execute_round) and the decoders' fast round executor (execute_round_owned).
 #pragma once
 
 #include "common.cuh"

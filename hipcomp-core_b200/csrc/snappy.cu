@@ -1,13 +1,18 @@
 // b200comp — batched Snappy raw-block codec for sm_100a.
 //
-// C ABI replaces reference src/lowlevel/SnappyBatch.cpp:84-245.  The encoder keeps
-// the reference's match policy (src/snappy/compression.hiph:190-385: 12-bit hash,
-// 32-position windows, nearest-lower-lane twin, uint16 table, <=64-byte copies)
-// so its output is the same byte stream, but one warp does search and emission
-// back to back (the reference ping-pongs two warps through __syncthreads()), and
-// several chunks share a CTA.  The decoder is one warp per chunk over the
-// element grammar of src/snappy/decompression_decode.hiph:72-150 (the reference
-// uses a 3-warp prefetch/decode/process pipeline with nanosleep spin queues).
+// C ABI replaces reference src/lowlevel/SnappyBatch.cpp:84-245.
+//
+// Encoders.  Chunks up to 64 KiB (every headline configuration) go to the team encoder of
+// lz_team_encode.cuh with the Snappy Emit policy below: one CTA per chunk, chunk and hash table
+// resident in shared memory.  Its streams are plain Snappy streams with a ratio above the
+// reference's, but not the reference's bytes.  Larger chunks (and callers that declare no chunk
+// size) keep the warp encoder below, which reproduces the reference's match policy
+// (src/snappy/compression.hiph:190-385: 12-bit hash, 32-position windows, nearest-lower-lane twin,
+// uint16 table, <= 64-byte copies) byte for byte - one warp does search and emission back to back
+// where the reference ping-pongs two warps through __syncthreads().
+// The decoder is one warp per chunk over the element grammar of
+// src/snappy/decompression_decode.hiph:72-150 (the reference uses a 3-warp prefetch / decode /
+// process pipeline with nanosleep spin queues); see lz4.cu and lz_common.cuh for the scheme.
 #include "lz_common.cuh"
 #include "lz_team_encode.cuh"
 
