@@ -1608,6 +1608,7 @@ hipcompStatus_t hipcompBatchedCascadedCompressAsync(const void* const* device_un
                                                     const hipcompBatchedCascadedOpts_t o, hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedCascadedCompressAsync()";
+  B200_TRACE(fn);
   if (batch_size == 0) return hipcompSuccess;
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
@@ -1652,6 +1653,7 @@ hipcompStatus_t hipcompBatchedCascadedDecompressAsync(const void* const* device_
                                                       hipcompStatus_t* device_statuses, hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedCascadedDecompressAsync()";
+  B200_TRACE(fn);
   if (batch_size == 0) return hipcompSuccess;
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
@@ -1677,6 +1679,7 @@ hipcompStatus_t hipcompBatchedCascadedGetDecompressSizeAsync(const void* const* 
                                                              hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedCascadedGetDecompressSizeAsync()";
+  B200_TRACE(fn);
   if (batch_size == 0) return hipcompSuccess;
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
@@ -1695,6 +1698,7 @@ hipcompStatus_t b200compBatchedCascadedSelectOptsAsync(const void* const* device
                                                        hipcompType_t type, uint8_t* device_opts, hipStream_t stream)
 {
   static const char* fn = "b200compBatchedCascadedSelectOptsAsync()";
+  B200_TRACE(fn);
   if (batch_size == 0) return hipcompSuccess;
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
@@ -1728,6 +1732,7 @@ hipcompStatus_t b200compBatchedCascadedCompressWithOptsAsync(const void* const* 
                                                              const uint8_t* device_opts, hipStream_t stream)
 {
   static const char* fn = "b200compBatchedCascadedCompressWithOptsAsync()";
+  B200_TRACE(fn);
   if (batch_size == 0) return hipcompSuccess;
   B200_CHECK_NOT_NULL(device_uncompressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);

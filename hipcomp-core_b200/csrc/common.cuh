@@ -54,6 +54,21 @@ inline bool device_accessible(const void* p)
                               "'" #ptr "': memory location is not accessible by the current GPU."); \
   } while (0)
 
+// NVTX range around every C-ABI call when the library is built with -DB200COMP_NVTX (make EXTRA=-DB200COMP_NVTX):
+// the calls show up by name on a timeline (the reference has no tracing).  Off by default: no cost.
+#ifdef B200COMP_NVTX
+}  // namespace b200comp
+#include <nvtx3/nvToolsExt.h>
+namespace b200comp {
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+#define B200_TRACE(fn) ::b200comp::NvtxRange b200_trace_range_(fn)
+#else
+#define B200_TRACE(fn) ((void)0)
+#endif
+
 inline hipcompStatus_t check_launch(const char* fn)
 {
   const cudaError_t e = cudaGetLastError();

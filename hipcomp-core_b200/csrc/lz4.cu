@@ -608,6 +608,7 @@ hipcompStatus_t hipcompBatchedLZ4CompressAsync(const void* const* device_uncompr
                                                hipcompBatchedLZ4Opts_t format_opts, hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedLZ4CompressAsync()";
+  B200_TRACE(fn);
   if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
     return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
   const uint32_t ht = (uint32_t)lz4::hash_table_size(max_uncompressed_chunk_bytes);
@@ -701,6 +702,7 @@ hipcompStatus_t hipcompBatchedLZ4DecompressAsync(const void* const* device_compr
                                                  hipcompStatus_t* device_statuses, hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedLZ4DecompressAsync()";
+  B200_TRACE(fn);
   if (batch_size == 0) return hipcompSuccess;
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
@@ -724,6 +726,7 @@ hipcompStatus_t hipcompBatchedLZ4GetDecompressSizeAsync(const void* const* devic
                                                         hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedLZ4GetDecompressSizeAsync()";
+  B200_TRACE(fn);
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);

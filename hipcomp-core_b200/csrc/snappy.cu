@@ -520,6 +520,7 @@ hipcompStatus_t hipcompBatchedSnappyGetDecompressSizeAsync(const void* const* de
                                                            hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedSnappyGetDecompressSizeAsync()";
+  B200_TRACE(fn);
   B200_CHECK_NOT_NULL(device_compressed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
@@ -539,6 +540,7 @@ hipcompStatus_t hipcompBatchedSnappyDecompressAsync(const void* const* device_co
                                                     hipcompStatus_t* device_statuses, hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedSnappyDecompressAsync()";
+  B200_TRACE(fn);
   B200_CHECK_NOT_NULL(device_compresed_ptrs, fn);
   B200_CHECK_NOT_NULL(device_compressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
@@ -579,6 +581,7 @@ hipcompStatus_t hipcompBatchedSnappyCompressAsync(const void* const* device_unco
                                                   hipStream_t stream)
 {
   static const char* fn = "hipcompBatchedSnappyCompressAsync()";
+  B200_TRACE(fn);
   B200_CHECK_NOT_NULL(device_uncompressed_ptr, fn);
   B200_CHECK_NOT_NULL(device_uncompressed_bytes, fn);
   B200_CHECK_NOT_NULL(device_compressed_ptr, fn);
