@@ -255,6 +255,7 @@ __device__ __forceinline__ bool read_lsic_bounded(const uint8_t* comp, uint32_t 
 // k decodes sequence k on its own, and the round executor (lz_common.cuh) produces the
 // output 64 bytes per iteration.
 constexpr int kWin = 512;
+constexpr uint32_t kWinKeep = 224; // a staged window is reused while at least this much of it lies ahead
 
 struct SlowRec {
   uint32_t lit_off, nlit, mlen, off;
@@ -288,11 +289,21 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
     const uintptr_t cbase = reinterpret_cast<uintptr_t>(comp);
     uint32_t ci = 0, di = 0;
     bool ok = true;
+    // the staged window [wpos, wpos + wvalid) and its step table stay valid across rounds: a round of 32
+    // sequences consumes ~200 of the 512 bytes, so about every second round starts without a load from global memory
+    uint32_t wpos = 0, wvalid = 0;
+    bool staged = false;
     while (ok && ci < comp_len) {
+      uint32_t shift = ci - wpos; // where the walk starts inside the window (wpos may lie up to 15 bytes below 0: wrap-safe)
+      const bool reuse = staged && shift < wvalid && (shift + kWinKeep <= wvalid || wpos + wvalid == comp_len);
+      const bool fresh = !reuse;
+      if (fresh) {
       // ---- stage [ci - shift, ci - shift + 512): 16-byte aligned blocks that intersect the stream
-      const uint32_t shift = (uint32_t)((cbase + ci) & 15);
-      const uint32_t wpos = ci - shift; // stream position of window byte 0 (may "underflow" by < 16 at ci = 0)
-      const uint32_t wvalid = min((uint32_t)kWin, comp_len - wpos);
+      shift = (uint32_t)((cbase + ci) & 15);
+      wpos = ci - shift; // stream position of window byte 0 (may "underflow" by < 16 at ci = 0)
+      wvalid = min((uint32_t)kWin, comp_len - wpos);
+      staged = true;
+      __syncwarp(); // the previous round's readers of the window are done
       uint4 v = make_uint4(0, 0, 0, 0);
       if (16u * lane < wvalid) v = ld_block16_guarded(cbase, comp_len, cbase + ci - shift + 16u * lane, win + 16 * lane);
       *reinterpret_cast<uint4*>(win + 16 * lane) = v;
@@ -310,6 +321,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
         }
         *reinterpret_cast<uint4*>(step + 16 * lane) = make_uint4(r[0], r[1], r[2], r[3]);
       }
+      } // fresh
       __syncwarp();
       const bool at_stream_end = wpos + wvalid == comp_len;
 
@@ -397,11 +409,11 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
           if (at_stream_end) {
             // the window already holds the rest of the stream: the header is truncated
             // (literal runs that pass the end were diagnosed above)
-            if (!(k == 0u && idx == shift)) break; // re-stage at this token first: cheap and uniform
+            if (!(k == 0u && fresh)) break; // re-stage at this token first: cheap and uniform
             ok = false;
             break;
           }
-          if (k == 0u && idx == shift) giant = true;
+          if (k == 0u && fresh) giant = true;
           break;
         }
         if (lane == k) {
@@ -413,6 +425,10 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
         ++k;
       }
       if (!ok) break;
+      if (k == 0u && !fresh) { // the token did not fit what is left of a reused window: stage at it
+        staged = false;
+        continue;
+      }
       if (giant) {
         // one sequence straight from global memory (long literal run and / or long headers)
         const uint32_t tok = __ldg(comp + ci);

@@ -205,6 +205,7 @@ __device__ __forceinline__ bool read_preamble(const uint8_t* comp, uint32_t comp
 // an extended length (>= 61 bytes) and elements that do not fit a fresh window run one at a time
 // from global memory with vector copies.
 constexpr int kWin = 512;
+constexpr uint32_t kWinKeep = 160; // a staged window is reused while at least this much of it lies ahead
 
 __global__ void __launch_bounds__(kDecWarps * 32)
 decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes, const size_t* out_caps,
@@ -235,12 +236,23 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
     if (!ok) size = 0;
     left = size;
     uint32_t dst = 0;
+    // the staged window [wpos, wpos + wvalid) and its step table stay valid across rounds: a round consumes
+    // ~120 of the 512 bytes, so three rounds out of four start without a load from global memory
+    uint32_t wpos = 0, wvalid = 0;
+    bool staged = false;
     while (ok && left > 0) {
       if (cur >= comp_len) { ok = false; break; }
+      // reuse while a good part of a round still lies inside the window (or the window ends with the stream)
+      uint32_t shift = cur - wpos; // where the walk starts inside the window (wpos may lie up to 15 bytes below 0: wrap-safe)
+      const bool reuse = staged && shift < wvalid && (shift + kWinKeep <= wvalid || wpos + wvalid == comp_len);
+      const bool fresh = !reuse;
+      if (fresh) {
       // ---- stage the window
-      const uint32_t shift = (uint32_t)((cbase + cur) & 15);
-      const uint32_t wpos = cur - shift;
-      const uint32_t wvalid = min((uint32_t)kWin, comp_len - wpos);
+      shift = (uint32_t)((cbase + cur) & 15);
+      wpos = cur - shift;
+      wvalid = min((uint32_t)kWin, comp_len - wpos);
+      staged = true;
+      __syncwarp(); // the previous round's readers of the window are done
       uint4 v = make_uint4(0, 0, 0, 0);
       if (16u * lane < wvalid) v = ld_block16_guarded(cbase, comp_len, cbase + cur - shift + 16u * lane, win + 16 * lane);
       *reinterpret_cast<uint4*>(win + 16 * lane) = v;
@@ -261,6 +273,7 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
         }
         *reinterpret_cast<uint4*>(step + 16 * lane) = make_uint4(r[0], r[1], r[2], r[3]);
       }
+      } // fresh
       __syncwarp();
 
       // ---- walk the element chain
@@ -276,6 +289,10 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
       }
       __syncwarp();
       const uint32_t my_idx = lane < k ? (uint32_t)idxs[lane] : 0u;
+      if (k == 0u && !fresh) { // the element did not fit what is left of a reused window: stage at it
+        staged = false;
+        continue;
+      }
       if (k == 0u) {
         // one element straight from global memory: extended literal, or an element cut by the window end
         uint32_t blen, offset = 0;
