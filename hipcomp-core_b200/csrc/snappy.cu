@@ -212,13 +212,14 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
                          void* const* out_ptrs, size_t* actual, hipcompStatus_t* statuses, size_t batch)
 {
   __shared__ __align__(16) uint8_t s_win[kDecWarps][kWin + 32];
-  __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin];
+  __shared__ __align__(16) uint8_t s_step[kDecWarps][kWin + 64]; // + 64 zero bytes: a walk that leaves the window stops
   __shared__ uint32_t s_own[kDecWarps][kOwnWords];           // start bitmap, bases and stage of the round executor
   __shared__ uint16_t s_idx[kDecWarps][32];                  // element positions found by the walk
   const uint32_t lane = (uint32_t)lane_id();
   const int warp = threadIdx.x >> 5;
   uint8_t* win = s_win[warp];
   uint8_t* step = s_step[warp];
+  reinterpret_cast<uint16_t*>(step + kWin)[lane_id()] = 0; // the pad behind the table (never written again)
   const size_t stride = (size_t)gridDim.x * kDecWarps;
   for (size_t chunk = (size_t)blockIdx.x * kDecWarps + warp; chunk < batch; chunk += stride) {
     const uint8_t* comp = static_cast<const uint8_t*>(comp_ptrs[chunk]);
@@ -272,18 +273,26 @@ decompress_window_kernel(const void* const* comp_ptrs, const size_t* comp_bytes,
           r[j] = (copy_step & is_copy) | (lit_step & ~is_copy);
         }
         *reinterpret_cast<uint4*>(step + 16 * lane) = make_uint4(r[0], r[1], r[2], r[3]);
+        // an element that does not end inside the window (or starts behind it) gets step 0 as well, so that the
+        // walk below tests one thing; only the lanes within 80 bytes of the window's end have such entries
+        if (16u * lane + 80u > wvalid) {
+#pragma unroll 1
+          for (uint32_t b = 0; b < 16u; ++b) {
+            const uint32_t p = 16u * lane + b;
+            if (p + step[p] > wvalid) step[p] = 0;
+          }
+        }
       }
       } // fresh
       __syncwarp();
 
-      // ---- walk the element chain
+      // ---- walk the element chain: one table byte per element, 0 = stop (extended literal, window end)
       uint32_t idx = shift, k = 0;
       uint16_t* idxs = s_idx[warp];
 #pragma unroll 8
       for (; k < 32u; ++k) {
-        if (idx >= wvalid) break;
-        const uint32_t s = step[idx];
-        if (s == 0u || idx + s > wvalid) break;
+        const uint32_t s = step[idx]; // idx < kWin + 61: inside the table or its zero pad
+        if (s == 0u) break;
         idxs[k] = (uint16_t)idx;
         idx += s;
       }
