@@ -52,6 +52,7 @@ EXT_PROTOTYPES = {
     "b200compGatherChunksAsync": [_vp, _vp, _vp, _vp, _sz, _vp],
     "b200compBatchedCascadedSelectOptsAsync": [_vp, _vp, _sz, C.c_int, _vp, _vp],
     "b200compBatchedCascadedCompressWithOptsAsync": [_vp, _vp, _sz, _vp, _vp, C.c_int, _vp, _vp],
+    "b200compBatchedLZ4CompressNoAllocAsync": [_vp, _vp, _sz, _sz, _vp, _vp, LZ4Opts, _vp],
     "b200compHostAlloc": [_sz, _vpp],
     "b200compStagerCreate": [C.c_int, _sz, _sz, _vp, C.c_int, _vpp],
     "b200compStagerCompress": [_vp, _vp, _sz, _vp, _vp, _szp],

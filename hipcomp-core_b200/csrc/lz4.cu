@@ -13,8 +13,11 @@
 #include "lz_common.cuh"
 #include "lz_team_encode.cuh"
 
+#include <mutex>
+
 #pragma GCC visibility push(default)
 #include "hipcomp/lz4.h"
+#include "hipcomp/b200_ext.h"
 #pragma GCC visibility pop
 
 namespace b200comp {
@@ -757,3 +760,62 @@ hipcompStatus_t hipcompBatchedLZ4GetDecompressSizeAsync(const void* const* devic
 }
 
 } // extern "C"
+
+// ---- Allocation-free compress entry point (include/hipcomp/b200_ext.h; no counterpart in the reference).
+// The hash tables that hipcompBatchedLZ4CompressAsync keeps in the caller's workspace for chunks above 64 KiB
+// live here in a static device array instead: one copy per GPU that loads the library, held until exit, shared
+// by every call.  The encoder resets a chunk's table before it uses it, so nothing has to be cleared between
+// calls; two calls that overlap on the GPU would share tables and race.
+static __device__ __align__(256) unsigned char g_lz4_noalloc_scratch[B200COMP_LZ4_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+// Device address of the scratch array on the current device.  The array's name is only a host-side stand-in in
+// host code: the address a kernel can use comes from cudaGetSymbolAddress, taken once per device with that
+// device current.
+cudaError_t noalloc_scratch(void** out)
+{
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_lz4_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return cudaSuccess;
+}
+} // namespace
+
+extern "C" hipcompStatus_t b200compBatchedLZ4CompressNoAllocAsync(
+    const void* const* device_uncompressed_ptrs, const size_t* device_uncompressed_bytes,
+    size_t max_uncompressed_chunk_bytes, size_t batch_size, void* const* device_compressed_ptrs,
+    size_t* device_compressed_bytes, hipcompBatchedLZ4Opts_t format_opts, hipStream_t stream)
+{
+  static const char* fn = "b200compBatchedLZ4CompressNoAllocAsync()";
+  if (max_uncompressed_chunk_bytes > lz4::kMaxChunk)
+    return fail(hipcompErrorInvalidValue, fn, "Maximum chunk size for LZ4 is " + std::to_string(lz4::kMaxChunk));
+  const size_t required = lz4::compress_temp_bytes(max_uncompressed_chunk_bytes, batch_size);
+  if (required > (size_t)B200COMP_LZ4_NOALLOC_SCRATCH_BYTES)
+    return fail(hipcompErrorInvalidValue, fn,
+                "Batch too large for the built-in scratch: " + std::to_string(batch_size) + " chunks of up to "
+                    + std::to_string(max_uncompressed_chunk_bytes) + " bytes need " + std::to_string(required)
+                    + " bytes of hash tables, the library holds " + std::to_string(B200COMP_LZ4_NOALLOC_SCRATCH_BYTES)
+                    + " (at most " + std::to_string(B200COMP_LZ4_NOALLOC_MAX_BATCH)
+                    + " chunks above 64 KiB per call; use hipcompBatchedLZ4CompressAsync with a workspace).");
+  void* scratch = nullptr;
+  const cudaError_t e = noalloc_scratch(&scratch);
+  if (e != cudaSuccess)
+    return fail(hipcompErrorCudaError, fn, std::string("cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+  return hipcompBatchedLZ4CompressAsync(device_uncompressed_ptrs, device_uncompressed_bytes,
+                                        max_uncompressed_chunk_bytes, batch_size, scratch,
+                                        (size_t)B200COMP_LZ4_NOALLOC_SCRATCH_BYTES, device_compressed_ptrs,
+                                        device_compressed_bytes, format_opts, stream);
+}

@@ -7,6 +7,7 @@
 #define HIPCOMP_B200_EXT_H
 
 #include "hipcomp.h"
+#include "hipcomp/lz4.h"
 
 #include <stdint.h>
 
@@ -43,6 +44,28 @@ hipcompStatus_t b200compBatchedCascadedCompressWithOptsAsync(const void* const* 
                                                              void* const* device_compressed_ptrs,
                                                              size_t* device_compressed_bytes, hipcompType_t type,
                                                              const uint8_t* device_opts, hipStream_t stream);
+
+/* ---- LZ4 compression that allocates nothing and takes no workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments, output bytes and errors as
+ * hipcompBatchedLZ4CompressAsync (lz4.h) without device_temp_ptr / temp_bytes: the per-chunk hash tables that
+ * call keeps in the caller's workspace for chunks above 64 KiB live in a static device array of
+ * B200COMP_LZ4_NOALLOC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until exit).
+ * Limit: hipcompBatchedLZ4CompressGetTempSize(batch_size, max_uncompressed_chunk_bytes) must not exceed that
+ * size, i.e. at most B200COMP_LZ4_NOALLOC_MAX_BATCH chunks per call when chunks are above 64 KiB (any batch size
+ * up to 64 KiB, where the encoder keeps its tables in shared memory); larger requests return
+ * hipcompErrorInvalidValue.  The call makes no cudaMalloc / cudaFree and no allocating library call.  All calls on
+ * one GPU share the array: calls that overlap on the GPU (different streams, or a second thread) race; calls
+ * ordered on one stream do not.  Nothing has to be cleared between calls - the encoder resets a chunk's table
+ * before it uses it. */
+#define B200COMP_LZ4_NOALLOC_SCRATCH_BYTES (16u << 20)
+#define B200COMP_LZ4_NOALLOC_MAX_BATCH 512u /* 16 MiB / (16384-entry uint16 table per chunk) */
+hipcompStatus_t b200compBatchedLZ4CompressNoAllocAsync(const void* const* device_uncompressed_ptrs,
+                                                       const size_t* device_uncompressed_bytes,
+                                                       size_t max_uncompressed_chunk_bytes, size_t batch_size,
+                                                       void* const* device_compressed_ptrs,
+                                                       size_t* device_compressed_bytes,
+                                                       hipcompBatchedLZ4Opts_t format_opts, hipStream_t stream);
 
 /* ---- Host-buffer staging pipeline (no reference counterpart: reference CHANGELOG.md:97-98 leaves
  * host <-> device staging to the caller).  One call per direction for data that lives in pinned host memory:
