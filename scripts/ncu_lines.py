@@ -21,7 +21,11 @@ top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", f"regex:{pat}"],
                      capture_output=True, text=True).stdout
 blocks = out.split('"Kernel Name",')
-blk = blocks[1]
+# ncu matches the bare function name only: NCU_LINES_MATCH=<substring> picks among template instantiations
+want = os.environ.get("NCU_LINES_MATCH")
+blk = next((b for b in blocks[1:] if want is None or want in b.splitlines()[0]), None)
+if blk is None:
+    sys.exit("no kernel in the report matches")
 kname = blk.splitlines()[0]
 rows = list(csv.reader(io.StringIO("\n".join(blk.splitlines()[1:]))))
 h = rows[0]
@@ -56,7 +60,7 @@ for f in os.listdir(tmp):
                 else:
                     cur = (os.path.basename(m.group(1)), int(m.group(2)))
                 continue
-            if re.match(r"\s+/\*[0-9a-f]{4}\*/", ln):
+            if re.match(r"\s+/\*[0-9a-f]{4,}\*/", ln):
                 seq.append(cur)
                 fresh = True
         if len(seq) == len(sass):
