@@ -671,6 +671,71 @@ __device__ void raw_copy(const T* in, size_t n, uint8_t* out)
   if (lane < (int)(padded - bytes)) dst[bytes + lane] = 0;
 }
 
+// Bytes the fused encoder emits for one full chunk (metadata + arrays, the advance of its cursor) when every element
+// is a run of its own and - for R = 2 - no two neighbouring deltas are equal, so that every run-length array is
+// all ones (8 bytes bit-packed) and the value array holds the N - 1 adjacent differences.  0 when the chunk is not
+// of that kind.  Kept out of line: it runs once per partition at most, and inlined it costs the common path
+// registers and instruction cache.
+template <int R>
+__device__ __noinline__ uint32_t distinct_chunk_bytes(const uint4* src, bool use_bp)
+{
+  constexpr uint32_t N = kChunkBytes / 4;
+  const int lane = lane_id();
+  uint4 v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = ld_stream16(src + lane + 32 * k);
+  int32_t dmn = 0x7fffffff, dmx = (int32_t)0x80000000;
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t zx = (lane == 0 && k < 7) ? v[k < 7 ? k + 1 : k].x : v[k].x;
+    const uint32_t nx = __shfl_sync(kFull, zx, (lane + 1) & 31);
+    const bool last = (k == 7 && lane == 31); // element N - 1: no successor, no delta
+    const int32_t d0 = (int32_t)(v[k].y - v[k].x), d1 = (int32_t)(v[k].z - v[k].y), d2 = (int32_t)(v[k].w - v[k].z);
+    const int32_t d3 = (int32_t)(nx - v[k].w);
+    ok = ok && d0 != 0 && d1 != 0 && d2 != 0 && (last || d3 != 0);
+    dmn = min(dmn, min(d0, min(d1, d2)));
+    dmx = max(dmx, max(d0, max(d1, d2)));
+    if (!last) {
+      dmn = min(dmn, d3);
+      dmx = max(dmx, d3);
+    }
+    if constexpr (R == 2) {
+      // the delta behind d3 is the first delta of the next lane's vector (of the next tile for lane 31)
+      const uint32_t zy = (lane == 0 && k < 7) ? v[k < 7 ? k + 1 : k].y : v[k].y;
+      const uint32_t ny = __shfl_sync(kFull, zy, (lane + 1) & 31);
+      const int32_t d4 = (int32_t)(ny - nx);
+      ok = ok && d0 != d1 && d1 != d2 && (last || (d2 != d3 && d3 != d4));
+    }
+  }
+  if (!__all_sync(kFull, ok)) return 0;
+  if (!use_bp) // raw arrays: R of 2-byte run lengths (N, then N - 1 of them), N - 1 values
+    return 12u + 4u * R + 2u * N + (R == 2 ? ((2u * (N - 1u) + 3u) & ~3u) : 0u) + 4u * (N - 1u);
+  dmn = __reduce_min_sync(kFull, dmn);
+  dmx = __reduce_max_sync(kFull, dmx);
+  const uint32_t vbw = 32u - (uint32_t)__clz((int)((uint32_t)dmx - (uint32_t)dmn));
+  return 12u + 4u * R + 8u * R + 8u + 4u * (((N - 1u) * vbw + 31u) >> 5);
+}
+
+// Look-ahead of the fused encoder behind a first chunk that turned out all distinct: lower bound of the partition's
+// compressed size - the chunk at s4 (the output cursor stands at chunk_start) and the more_full full chunks behind
+// it, exact where distinct_chunk_bytes knows, the smallest possible chunk otherwise.  Gives up when the chunk at
+// s4 is not of that kind.  True when the partition cannot fit (it is stored raw).
+template <int R>
+__device__ __noinline__ bool partition_cannot_fit(const uint4* s4, size_t chunk_start, size_t limit, bool use_bp,
+                                                  int more_full, bool ragged_tail)
+{
+  constexpr uint32_t kMeta = 12 + 4 * R;
+  const uint32_t floor_bytes = kMeta + (use_bp ? 8u * (R + 1) : 4u); // the smallest chunk: one run
+  size_t total = chunk_start + (ragged_tail ? kMeta : 0u);
+  for (int j = 0; j <= more_full && total <= limit; ++j) {
+    const uint32_t exact = distinct_chunk_bytes<R>(s4 + 256 * j, use_bp);
+    if (j == 0 && exact == 0) return false; // not of that kind: no look-ahead
+    total += exact ? exact : floor_bytes;
+  }
+  return total > limit;
+}
+
 // Fused fast path for the headline option set (num_RLEs = 1, num_deltas = 1, 4-byte elements, full
 // 4096-byte chunk, 16-byte aligned source).  Same bytes as the generic layer loop, different data
 // movement: the chunk never sits in shared memory.  Each lane keeps 8 coalesced 16-byte vectors
@@ -681,7 +746,7 @@ __device__ void raw_copy(const T* in, size_t n, uint8_t* out)
 // Returns false when the chunk does not fit (caller falls back to the raw partition).
 template <typename T, int R>
 __device__ bool compress_chunk_rd1(const T* src, uint8_t* out, size_t& cur, size_t limit, bool use_bp, T* A,
-                                   uint16_t* C)
+                                   uint16_t* C, int& runs)
 {
   static_assert(sizeof(T) == 4, "fast path is for 4-byte elements");
   constexpr int N = kChunkBytes / 4;
@@ -741,6 +806,7 @@ __device__ bool compress_chunk_rd1(const T* src, uint8_t* out, size_t& cur, size
     base += tt;
   }
   const int m = (int)base; // number of runs, >= 1
+  runs = m;
   __syncwarp();
 
   // ends -> lengths, values -> deltas, rewritten in place in swizzled order: the swizzle permutes inside a
@@ -891,8 +957,17 @@ __device__ void compress_partition(const T* in, size_t in_bytes, uint8_t* out, s
   for (size_t c = 0; c < n_chunks && use_compression; ++c) {
     if constexpr (sizeof(T) == 4) {
       if (fast_r1d1 && n_total - c * N >= (size_t)N) {
-        const bool fits = compress_chunk_rd1<T, kR2 ? 2 : 1>(in + c * N, out, cur, limit, bp != 0, A, C);
+        int runs = 0;
+        const bool fits = compress_chunk_rd1<T, kR2 ? 2 : 1>(in + c * N, out, cur, limit, bp != 0, A, C, runs);
         if (!fits) use_compression = false;
+        // Incompressible partitions (random words): the layer code finds out that the partition does not fit
+        // only after compacting and packing chunk after chunk - a chunk of random words grows by 28 bytes, so
+        // the verdict falls on the partition's last chunk.  When the first chunk turns out all distinct, the
+        // sizes of the chunks behind it are added up before any of them is encoded.
+        else if (c == 0 && runs == N && n_total >= 2 * (size_t)N &&
+                 partition_cannot_fit<kR2 ? 2 : 1>(reinterpret_cast<const uint4*>(in + N), cur, limit, bp != 0,
+                                                   (int)(n_total / N - 2), (n_total % N) != 0))
+          use_compression = false;
         continue;
       }
     }
@@ -1119,16 +1194,18 @@ __device__ bool decompress_chunk_r1d1(const uint8_t* chunk_ptr, uint32_t avail_w
 // decompress_chunk_r1d1: deltas are added onto the run starts of a zeroed array O, one register prefix sum
 // produces the 1024 outputs.  O must not alias A.  Returns false before writing anything to global memory
 // when a precondition fails (the generic layers then continue from the untouched A).
-template <typename T>
+template <typename T, bool kSmemCounts = false>
 __device__ bool decompress_tail_d1(const uint8_t* counts_ptr, uint32_t cb, const T* A, int nv, T seed, T* gout,
                                    uint32_t* O)
 {
+  // kSmemCounts: the caller has staged the run lengths in shared memory (plain loads instead of __ldg)
+  auto ldw = [](const uint32_t* p) { return kSmemCounts ? *p : __ldg(p); };
   static_assert(sizeof(T) == 4, "4-byte elements");
   constexpr uint32_t N = kChunkBytes / 4;
   const int lane = lane_id();
   if (cb < 8 || (cb & 3)) return false;
   const uint32_t* cw = reinterpret_cast<const uint32_t*>(counts_ptr);
-  const uint32_t cfr = __ldg(cw), cmeta = __ldg(cw + 1);
+  const uint32_t cfr = ldw(cw), cmeta = ldw(cw + 1);
   const uint32_t cbw = cmeta >> 16, nc = cmeta & 0xffffu;
   const int m = nv + 1;
   if (nc > N || cbw > 16 || (uint32_t)m > N || nc < (uint32_t)m) return false;
@@ -1145,13 +1222,13 @@ __device__ bool decompress_tail_d1(const uint8_t* counts_ptr, uint32_t cb, const
     if (r0 < m) {
       const uint32_t cp = (uint32_t)r0 * cbw;
       // the word after the last packed word is inside the chunk (the next array's header follows)
-      const uint32_t cv = __funnelshift_r(__ldg(cw + 2 + (cp >> 5)), __ldg(cw + 3 + (cp >> 5)), cp & 31) & cmask;
+      const uint32_t cv = __funnelshift_r(ldw(cw + 2 + (cp >> 5)), ldw(cw + 3 + (cp >> 5)), cp & 31) & cmask;
       len0 = (uint32_t)(uint16_t)(cv + cfr);
       d0 = r0 == 0 ? seed : A[Swz<T>::p(r0 - 1)];
     }
     if (r1 < m) {
       const uint32_t cp = (uint32_t)r1 * cbw;
-      const uint32_t cv = __funnelshift_r(__ldg(cw + 2 + (cp >> 5)), __ldg(cw + 3 + (cp >> 5)), cp & 31) & cmask;
+      const uint32_t cv = __funnelshift_r(ldw(cw + 2 + (cp >> 5)), ldw(cw + 3 + (cp >> 5)), cp & 31) & cmask;
       len1 = (uint32_t)(uint16_t)(cv + cfr);
       d1 = A[Swz<T>::p(r1 - 1)];
     }
@@ -1208,6 +1285,136 @@ __device__ bool decompress_tail_d1(const uint8_t* counts_ptr, uint32_t cb, const
   return true;
 }
 
+// Fused decoder for num_RLEs = 2, num_deltas = 1, bit-packed, 4-byte elements (the library's default option
+// set), full chunk, 16-byte aligned destination.  The second run-length layer (values2, counts2) expands to the
+// deltas of the first layer; like the last stage, that expansion is a scatter plus a prefix sum: run k of layer 2
+// stores values2[k] - values2[k - 1] at its start position in a zeroed array E, and the running sum of E is the
+// delta array.  Runs of layer 2 are never empty in an encoder's stream (starts are distinct: plain stores); a
+// stream with one is left to the generic layers, which report it.
+// Shared memory: the compressed chunk is staged in Y (the C + I regions) by one round of coalesced loads, E and
+// then the deltas live in X (the A region); the first layer's run lengths are then moved behind the deltas so
+// that Y can become the accumulator array of decompress_tail_d1, which finishes the chunk.
+// Returns false before anything is written to global memory.
+template <typename T>
+__device__ bool decompress_chunk_r2d1(const uint8_t* chunk_ptr, uint32_t avail_words, T* gout, T* X, uint32_t* Y,
+                                      uint32_t& chunk_bytes)
+{
+  static_assert(sizeof(T) == 4, "4-byte elements");
+  constexpr uint32_t N = kChunkBytes / 4;
+  constexpr uint32_t kStageWords = 1024;
+  const int lane = lane_id();
+  const uint32_t* gw = reinterpret_cast<const uint32_t*>(chunk_ptr);
+  if (avail_words < 5) return false;
+  const uint32_t first = avail_words < 256u ? avail_words : 256u;
+  uint32_t w[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) w[k] = (uint32_t)(lane + 32 * k) < first ? __ldg(gw + lane + 32 * k) : 0u;
+  __syncwarp(); // earlier readers of X / Y are done
+#pragma unroll
+  for (int k = 0; k < 8; ++k) Y[lane + 32 * k] = w[k];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) reinterpret_cast<uint4*>(X)[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+  __syncwarp();
+  chunk_bytes = Y[0];
+  const uint32_t cb1 = Y[1], cb2 = Y[2], vb = Y[3];
+  const T seed = (T)Y[4];
+  if (cb1 < 8 || cb2 < 8 || vb < 8 || ((cb1 | cb2 | vb) & 3) || cb1 > 4096 || cb2 > 4096 || vb > 4096) return false;
+  const uint32_t w1 = 5, w2 = w1 + (cb1 >> 2), wv = w2 + (cb2 >> 2);
+  const uint32_t need = wv + (vb >> 2); // words of metadata + the three arrays
+  if (need > avail_words || need + 1 > kStageWords) return false; // + 1: the unpack may touch one word more
+  if (need > 256u) {
+    for (uint32_t i = 256u + (uint32_t)lane; i < need; i += 32) Y[i] = __ldg(gw + i);
+    __syncwarp();
+  }
+  const uint32_t* c2 = Y + w2;
+  const uint32_t* vw = Y + wv;
+  const uint32_t c2fr = c2[0], c2meta = c2[1], vfr = vw[0], vmeta = vw[1];
+  const uint32_t c2bw = c2meta >> 16, n2c = c2meta & 0xffffu, vbw = vmeta >> 16, n2 = vmeta & 0xffffu;
+  if (n2c > N || c2bw > 16 || n2 > N || vbw > 32 || n2c < n2) return false;
+  const uint32_t c2words = (n2c * c2bw + 31u) >> 5, vwords = (n2 * vbw + 31u) >> 5;
+  if (8u + 4u * c2words > cb2 || 8u + 4u * vwords > vb) return false;
+  const uint32_t c2mask = (1u << c2bw) - 1u, vmask = vbw >= 32 ? ~0u : (1u << vbw) - 1u;
+
+  uint32_t carry = 0, prev_val = 0;
+  for (uint32_t u = 0; u * 64 < n2; ++u) {
+    const uint32_t r0 = 64 * u + (uint32_t)lane, r1 = r0 + 32;
+    uint32_t len0 = 0, len1 = 0, val0 = 0, val1 = 0;
+    // a value that straddles two words has its second word inside its array; otherwise the extra word read is
+    // masked off (it is still inside Y)
+    if (r0 < n2) {
+      const uint32_t cp = r0 * c2bw, vp = r0 * vbw;
+      const uint32_t cv = __funnelshift_r(c2[2 + (cp >> 5)], c2[3 + (cp >> 5)], cp & 31) & c2mask;
+      const uint32_t vv = __funnelshift_r(vw[2 + (vp >> 5)], vw[3 + (vp >> 5)], vp & 31) & vmask;
+      len0 = (uint32_t)(uint16_t)(cv + c2fr);
+      val0 = vv + vfr;
+    }
+    if (r1 < n2) {
+      const uint32_t cp = r1 * c2bw, vp = r1 * vbw;
+      const uint32_t cv = __funnelshift_r(c2[2 + (cp >> 5)], c2[3 + (cp >> 5)], cp & 31) & c2mask;
+      const uint32_t vv = __funnelshift_r(vw[2 + (vp >> 5)], vw[3 + (vp >> 5)], vp & 31) & vmask;
+      len1 = (uint32_t)(uint16_t)(cv + c2fr);
+      val1 = vv + vfr;
+    }
+    // an empty run (or an absurd length) is not an encoder's stream
+    if (__any_sync(kFull, (r0 < n2 && (len0 == 0 || len0 > N)) || (r1 < n2 && (len1 == 0 || len1 > N)))) return false;
+    const uint32_t packed = len0 | (len1 << 16);
+    uint32_t incl = packed;
+#pragma unroll
+    for (int dd = 1; dd < 32; dd <<= 1) {
+      const uint32_t o = __shfl_up_sync(kFull, incl, dd);
+      if (lane >= dd) incl += o;
+    }
+    const uint32_t tot = __shfl_sync(kFull, incl, 31);
+    const uint32_t ex = incl - packed;
+    const uint32_t start0 = carry + (ex & 0xffffu);
+    const uint32_t start1 = carry + (tot & 0xffffu) + (ex >> 16);
+    carry += (tot & 0xffffu) + (tot >> 16);
+    if (carry > N - 1) return false; // the deltas of N outputs are at most N - 1
+    uint32_t p0 = __shfl_up_sync(kFull, val0, 1), p1 = __shfl_up_sync(kFull, val1, 1);
+    const uint32_t l0 = __shfl_sync(kFull, val0, 31);
+    if (lane == 0) {
+      p0 = prev_val;
+      p1 = l0;
+    }
+    prev_val = __shfl_sync(kFull, val1, 31);
+    if (r0 < n2) X[Swz<T>::p((int)start0)] = (T)(val0 - p0);
+    if (r1 < n2) X[Swz<T>::p((int)start1)] = (T)(val1 - p1);
+  }
+  const int nv = (int)carry; // number of first-layer deltas
+  __syncwarp();
+  // running sum of E, 128 elements per step, in place
+  uint32_t run = 0;
+  for (int base = 0; base < nv; base += 128) {
+    const int i0 = base + lane * 4;
+    Vec<T> v = ld_vec<T>(X, i0);
+    v.e[1] += v.e[0];
+    v.e[2] += v.e[1];
+    v.e[3] += v.e[2];
+    uint32_t incl = (uint32_t)v.e[3];
+#pragma unroll
+    for (int dd = 1; dd < 32; dd <<= 1) {
+      const uint32_t o = __shfl_up_sync(kFull, incl, dd);
+      if (lane >= dd) incl += o;
+    }
+    const uint32_t ex = incl - (uint32_t)v.e[3] + run;
+    run += __shfl_sync(kFull, incl, 31);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v.e[j] += (T)ex;
+    st_vec<T>(X, i0, v);
+  }
+  // the first layer's run lengths move behind the deltas (when there is room) and Y becomes the accumulator array
+  const uint32_t c1w = (cb1 >> 2) + 1; // + the word an unpack may touch behind the array
+  const uint32_t at = ((uint32_t)nv + 127u) & ~127u;
+  if (at + c1w > N) {
+    __syncwarp();
+    return decompress_tail_d1<T, false>(reinterpret_cast<const uint8_t*>(gw + w1), cb1, X, nv, seed, gout, Y);
+  }
+  uint32_t* c1 = reinterpret_cast<uint32_t*>(X) + at;
+  for (uint32_t i = (uint32_t)lane; i < c1w; i += 32) c1[i] = Y[w1 + i];
+  __syncwarp();
+  return decompress_tail_d1<T, true>(reinterpret_cast<const uint8_t*>(c1), cb1, X, nv, seed, gout, Y);
+}
+
 // One warp decompresses one partition.  (reference cascaded_decompression_fcn :1106-1435)
 template <typename T, bool kTail>
 __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* out, size_t out_cap,
@@ -1260,6 +1467,20 @@ __device__ void decompress_partition(const uint8_t* comp, size_t comp_bytes, T* 
             chunk = (chunk + (cbytes & ~3u) + W - 1) / W * W;
             continue;
           }
+        }
+      }
+      if constexpr (kTail && sizeof(T) == 4) {
+        if (R == 2 && D == 1 && bp != 0 && n_total - done >= (size_t)N &&
+            (reinterpret_cast<uintptr_t>(out + done) & 15) == 0) {
+          uint32_t cbytes;
+          if (decompress_chunk_r2d1<T>(comp + chunk, (uint32_t)((end - chunk) >> 2), out + done, A,
+                                       reinterpret_cast<uint32_t*>(C), cbytes)) {
+            done += (size_t)N;
+            if (cbytes < (uint32_t)msize) { ok = false; break; }
+            chunk = (chunk + (cbytes & ~3u) + W - 1) / W * W;
+            continue;
+          }
+          __syncwarp();
         }
       }
       const uint32_t* mw = reinterpret_cast<const uint32_t*>(comp + chunk);

@@ -229,6 +229,82 @@ def test_cascaded_bit_exact_with_oracle(type_id, opts):
         assert dec[i].tobytes() == c.tobytes()
 
 
+@pytest.mark.parametrize("opts", [(1, 1, 1), (2, 1, 1), (1, 1, 0), (2, 1, 0)])
+def test_cascaded_incompressible_and_default_option_fast_paths(opts):
+    """The encoder's look-ahead on partitions whose first chunk is all distinct (sizes added up from the adjacent
+    differences before anything is encoded) and the fused num_RLEs = 2 decoder: same bytes as the oracle on the
+    cases that steer them."""
+    g = _g()
+    rng = np.random.default_rng(sum(opts) + 77)
+    n = 1024
+    parts = [
+        rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32),           # one chunk, does not fit
+        rng.integers(0, 1 << 32, 2 * n, dtype=np.uint64).astype(np.uint32),       # first chunk of two does not fit
+        rng.integers(0, 1 << 32, n + 5, dtype=np.uint64).astype(np.uint32),       # full chunk + ragged tail
+        rng.permutation(1 << 20)[:n].astype(np.uint32),                           # all distinct, 21-bit deltas: fits
+        rng.permutation(1 << 12)[: 3 * n].astype(np.uint32),                      # all distinct, small range
+        (np.arange(n) * 3 + 11).astype(np.uint32),                                # all distinct, every delta equal
+        np.cumsum(np.tile([1, 1, 2, 5, 5, 5, 9, 1], n // 8)).astype(np.uint32),   # all distinct, deltas repeat in places
+        np.cumsum(rng.integers(1, 3, 4 * n)).astype(np.uint32),                   # all distinct, deltas 1 or 2
+        np.concatenate([rng.integers(0, 1 << 32, n - 2, dtype=np.uint64).astype(np.uint32), [7, 7]]).astype(np.uint32),
+        np.concatenate([[5, 5], rng.integers(0, 1 << 32, n - 2, dtype=np.uint64).astype(np.uint32)]).astype(np.uint32),
+        datagen.sorted_ints(8 * n, 5).astype(np.uint32),                          # the usual compressible column
+        np.repeat(rng.integers(0, 1000, 400), rng.integers(1, 9, 400))[: 2 * n].astype(np.uint32),  # runs in both layers
+    ]
+    # the last delta pair of a chunk (elements N-3 .. N-1) equal / the pair that straddles two lanes equal
+    x = rng.permutation(1 << 24)[:n].astype(np.int64)
+    x[-1] = 2 * x[-2] - x[-3]
+    parts.append(x.astype(np.uint32))
+    y = rng.permutation(1 << 24)[:n].astype(np.int64)
+    y[5] = 2 * y[4] - y[3]
+    parts.append(y.astype(np.uint32))
+    chunks = [p.view(np.uint8) for p in parts]
+    co = g.L.CascadedOpts(4096, g.L.TYPE_UINT, *opts)
+    comp, dec, status, sizes, actual = g.roundtrip("cascaded", chunks, opts=co)
+    for i, c in enumerate(chunks):
+        exp = o.casc_compress(c, g.L.TYPE_UINT, *opts)
+        assert comp[i].tobytes() == exp.tobytes(), f"partition {i} ({len(c)} B) compressed bytes differ from oracle"
+        assert sizes[i] == len(c) and status[i] == 0 and actual[i] == len(c)
+        assert dec[i].tobytes() == c.tobytes()
+    # destinations that are only 4-byte aligned
+    src = g.B.DeviceBatch.from_host(chunks[:3])
+    stride = (g.B.max_compressed_chunk_bytes("cascaded", 8192 + 64, co) + 15) // 16 * 16
+    out = g.B.DeviceBatch.empty(src.n, stride)
+    shifted = g.B.DeviceBatch(out.buf, out.offsets + 4, np.full(src.n, stride - 4, np.int64))
+    comp2 = g.B.compress("cascaded", src, opts=co, max_chunk=8192 + 64, out=shifted)
+    torch.cuda.synchronize()
+    for got, c in zip(comp2.to_host(), chunks[:3]):
+        assert got.tobytes() == o.casc_compress(c, g.L.TYPE_UINT, *opts).tobytes()
+
+
+def test_cascaded_default_options_decoder_rejects_what_the_generic_layers_reject():
+    """Streams the fused num_RLEs = 2 decoder hands back to the generic layers: an empty run in the second layer,
+    truncated arrays; statuses and sizes equal the oracle's."""
+    g = _g()
+    x = datagen.sorted_ints(1024, 9).astype(np.uint32)
+    good = o.casc_compress(x.view(np.uint8), g.L.TYPE_UINT, 2, 1, 1)
+    cases = [good.copy()]
+    for cut in range(8, len(good), 37):
+        cases.append(good[:cut].copy())
+    n_exact = len(cases)  # whole + truncated: the verdict equals the oracle's
+    for word in range(2, min(len(good) // 4, 40)):
+        for flip in (0x1, 0x10000, 0xFFFF):
+            bad = good.copy()
+            bad.view(np.uint32)[word] ^= flip
+            cases.append(bad)
+    out, actual, status = g.decode_raw("cascaded", cases, [4096] * len(cases))
+    st, ac = status.cpu().numpy(), actual.cpu().numpy()
+    host = out.to_host(np.maximum(ac, 0))
+    for i, c in enumerate(cases):
+        est, eout = o.casc_decompress(c, 4096, 4)
+        if i < n_exact:
+            assert (st[i] == 0) == (est == 0), f"case {i}"
+        # damaged header words: never a fault, and a stream both accept decodes to the same bytes
+        assert st[i] in (0, 12)
+        if est == 0 and st[i] == 0:
+            assert ac[i] == len(eout) and host[i].tobytes() == eout.tobytes(), f"case {i}"
+
+
 def test_cascaded_reference_kat_words():
     """tests/test_cascaded_batch.cpp:336-378 through the C ABI (int32, RLE=2, delta=1, no bit-packing)."""
     g = _g()
