@@ -447,6 +447,85 @@ __device__ int rle_encode(T* vals, int n, uint16_t* counts)
   return m;
 }
 
+// rle_encode for the second layer of the fused R = 2 path (4-byte values): the same passes, which also leave the
+// signed minimum / maximum of the run values and of the run lengths (what write_array would scan for again).
+template <typename T, int N>
+__device__ int rle_encode_minmax(T* vals, int n, uint16_t* counts, int32_t& vmn, int32_t& vmx, int32_t& cmn,
+                                 int32_t& cmx)
+{
+  static_assert(sizeof(T) == 4, "4-byte values");
+  using Z = Swz<T>;
+  using ZC = Swz<uint16_t>;
+  constexpr int VE = Z::VE;
+  constexpr int TILE = 32 * VE;
+  const int lane = lane_id();
+  int32_t lvmn = 0x7fffffff, lvmx = (int32_t)0x80000000, lcmn = 0x7fffffff, lcmx = (int32_t)0x80000000;
+  int m = 0;
+  for (int base = 0; base < n; base += TILE) {
+    const int i0 = base + lane * VE;
+    const Vec<T> v = ld_vec<T>(vals, i0);
+    T nx = shfl_down_t(v.e[0], 1);
+    const int after = base + TILE < N ? base + TILE : N - 1;
+    const T nb = vals[Z::p(after)]; // first element of the next tile (broadcast read)
+    if (lane == 31) nx = nb;
+    uint32_t flags = 0;
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      const int i = i0 + j;
+      const T next = j + 1 < VE ? v.e[j + 1 < VE ? j + 1 : j] : nx;
+      const bool f = i < n && (i + 1 == n || next != v.e[j]);
+      flags |= (f ? 1u : 0u) << j;
+    }
+    int total;
+    int pos = m + warp_excl_sum<int>(__popc(flags), total);
+    __syncwarp(); // every lane has read its tile before anyone compacts into it
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      if (flags & (1u << j)) {
+        vals[Z::p(pos)] = v.e[j];
+        counts[ZC::p(pos)] = (uint16_t)(i0 + j + 1);
+        lvmn = min(lvmn, (int32_t)v.e[j]);
+        lvmx = max(lvmx, (int32_t)v.e[j]);
+        ++pos;
+      }
+    }
+    m += total;
+    __syncwarp();
+  }
+  // ends -> lengths, 64 runs per step (the swizzle permutes inside 64-element blocks of counts)
+  uint32_t carry = 0;
+  for (int u = 0; u * 64 < m; ++u) {
+    const int r0 = 64 * u + lane, r1 = r0 + 32;
+    const uint32_t e0 = r0 < m ? (uint32_t)counts[ZC::p(r0)] : 0u;
+    const uint32_t e1 = r1 < m ? (uint32_t)counts[ZC::p(r1)] : 0u;
+    uint32_t q0 = __shfl_up_sync(kFull, e0, 1);
+    uint32_t q1 = __shfl_up_sync(kFull, e1, 1);
+    const uint32_t l0 = __shfl_sync(kFull, e0, 31);
+    if (lane == 0) {
+      q0 = carry;
+      q1 = l0;
+    }
+    carry = __shfl_sync(kFull, r1 < m ? e1 : e0, 31);
+    const int32_t c0 = (int32_t)(int16_t)(e0 - q0), c1 = (int32_t)(int16_t)(e1 - q1);
+    if (r0 < m) {
+      counts[ZC::p(r0)] = (uint16_t)c0;
+      lcmn = min(lcmn, c0);
+      lcmx = max(lcmx, c0);
+    }
+    if (r1 < m) {
+      counts[ZC::p(r1)] = (uint16_t)c1;
+      lcmn = min(lcmn, c1);
+      lcmx = max(lcmx, c1);
+    }
+  }
+  __syncwarp();
+  vmn = __reduce_min_sync(kFull, lvmn);
+  vmx = __reduce_max_sync(kFull, lvmx);
+  cmn = __reduce_min_sync(kFull, lcmn);
+  cmx = __reduce_max_sync(kFull, lcmx);
+  return m;
+}
+
 // In-place adjacent differences: vals[i] = vals[i+1]-vals[i] for i < n-1.
 // Returns the seed vals[0].  (reference block_delta_compress :317-328)
 template <typename T, int N>
@@ -874,12 +953,29 @@ __device__ bool compress_chunk_rd1(const T* src, uint8_t* out, size_t& cur, size
     }
     cur += (ob_counts + 3u) & ~3u;
     __syncwarp();
-    const int n2 = rle_encode<T, N>(A, m - 1, C);
     uint32_t ob_counts2;
-    if (!write_array<uint16_t, N>(C, n2, out + cur, limit - cur, use_bp, ob_counts2)) return false;
-    cur += (ob_counts2 + 3u) & ~3u;
-    if (!write_array<T, N>(A, n2, out + cur, limit - cur, use_bp, ob_vals)) return false;
-    cur += (ob_vals + 3u) & ~3u;
+    if (use_bp) {
+      // the second layer's scan leaves min / max of both arrays: blocked packing without a second look
+      int32_t v2mn, v2mx, c2mn, c2mx;
+      const int n2 = rle_encode_minmax<T, N>(A, m - 1, C, v2mn, v2mx, c2mn, c2mx);
+      if (n2 == 0) v2mn = v2mx = c2mn = c2mx = 0; // empty arrays: frame 0, width 0
+      const int rp = (n2 & ~31) + lane; // padding up to the next multiple of 32 packs as zero
+      if (rp >= n2 && (n2 & 31)) {
+        C[Swz<uint16_t>::p(rp)] = (uint16_t)c2mn;
+        A[Swz<T>::p(rp)] = (T)v2mn;
+      }
+      __syncwarp();
+      if (!write_packed_known<uint16_t>(C, n2, c2mn, c2mx, out + cur, limit - cur, ob_counts2)) return false;
+      cur += (ob_counts2 + 3u) & ~3u;
+      if (!write_packed_known<T>(A, n2, v2mn, v2mx, out + cur, limit - cur, ob_vals)) return false;
+      cur += (ob_vals + 3u) & ~3u;
+    } else {
+      const int n2 = rle_encode<T, N>(A, m - 1, C);
+      if (!write_array<uint16_t, N>(C, n2, out + cur, limit - cur, false, ob_counts2)) return false;
+      cur += (ob_counts2 + 3u) & ~3u;
+      if (!write_array<T, N>(A, n2, out + cur, limit - cur, false, ob_vals)) return false;
+      cur += (ob_vals + 3u) & ~3u;
+    }
     if (lane == 0) {
       uint32_t* mw = reinterpret_cast<uint32_t*>(out + chunk_start);
       mw[0] = (uint32_t)(cur - chunk_start);
