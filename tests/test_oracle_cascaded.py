@@ -141,3 +141,107 @@ def test_truncation_never_succeeds_wrongly():
     for cut in range(0, len(comp), 97):
         st, back = o.casc_decompress(comp[:cut], x.nbytes, 4)
         assert st == o.CANNOT_DECOMPRESS and len(back) == 0
+
+
+# ---- the GPU encoder's look-ahead for incompressible partitions (csrc/cascaded.cu: distinct_chunk_bytes,
+# partition_cannot_fit) restated in numpy and held against the oracle: for a chunk of all-distinct elements the
+# formula must give exactly the bytes the format spends on that chunk, and the verdict "cannot fit" must agree
+# with the oracle falling back to a raw partition.
+def distinct_chunk_bytes_model(x, R, use_bp):
+    """x: one full chunk of 1024 uint32.  Bytes of the chunk (metadata + arrays), or 0 when the chunk is not
+    all distinct (R = 2: or two neighbouring deltas are equal)."""
+    n = 1024
+    assert len(x) == n
+    d = (x[1:].astype(np.int64) - x[:-1].astype(np.int64)).astype(np.uint32).view(np.int32).astype(np.int64)
+    if (d == 0).any():
+        return 0
+    if R == 2 and (d[1:] == d[:-1]).any():
+        return 0
+    if not use_bp:
+        return 12 + 4 * R + 2 * n + (up(2 * (n - 1), 4) if R == 2 else 0) + 4 * (n - 1)
+    span = int(d.max() - d.min()) & 0xFFFFFFFF
+    vbw = span.bit_length()
+    return 12 + 4 * R + 8 * R + 8 + 4 * (((n - 1) * vbw + 31) >> 5)
+
+
+def partition_cannot_fit_model(x, R, use_bp):
+    """x: a partition of uint32 (>= 2 full chunks) whose first chunk is all distinct; the verdict of the look-ahead
+    that runs behind the (encoded) first chunk."""
+    n = 1024
+    limit = 8 + up(4 * len(x), 4)
+    meta = 12 + 4 * R
+    floor_bytes = meta + (8 * (R + 1) if use_bp else 4)
+    first = distinct_chunk_bytes_model(x[:n], R, use_bp)
+    assert first, "the model is called for partitions whose first chunk the encoder found all distinct and exact"
+    total = 8 + first + (meta if len(x) % n else 0)
+    for j in range(1, len(x) // n):
+        exact = distinct_chunk_bytes_model(x[j * n:(j + 1) * n], R, use_bp)
+        if j == 1 and exact == 0:
+            return False
+        total += exact if exact else floor_bytes
+        if total > limit:
+            return True
+    return total > limit
+
+
+@pytest.mark.parametrize("opts", [(1, 1, 1), (2, 1, 1), (1, 1, 0), (2, 1, 0)])
+def test_lookahead_chunk_size_formula_equals_the_oracle(opts):
+    R, D, bp = opts
+    rng = np.random.default_rng(100 + R + 2 * bp)
+    for trial in range(60):
+        bits = int(rng.integers(11, 33))
+        if bits <= 16:
+            x = rng.permutation(1 << bits)[:1024].astype(np.uint32)
+        else:  # distinct with overwhelming probability; the model returns 0 (skipped) otherwise
+            x = rng.integers(0, 1 << bits, 1024, dtype=np.uint64).astype(np.uint32)
+        want = distinct_chunk_bytes_model(x, R, bp)
+        if want == 0:
+            continue
+        # a partition of this chunk plus a constant chunk (which always fits in a few bytes): when the oracle
+        # keeps the partition compressed, the first chunk's metadata word 0 is its size
+        part = np.concatenate([x, np.full(1024, 7, np.uint32)])
+        comp = o.casc_compress(part.view(np.uint8), 5, R, D, bp)
+        w = comp.view(np.uint32)
+        if (w[0] & 0xFFFFFF) == 0:  # raw: then the chunk alone must already overflow the partition's budget
+            assert 8 + want + (12 + 4 * R) > 8 + 8192 or not bp
+            continue
+        assert w[2] == want, f"trial {trial}: chunk bytes {w[2]} vs formula {want}"
+
+
+@pytest.mark.parametrize("opts", [(1, 1, 1), (2, 1, 1), (1, 1, 0), (2, 1, 0)])
+def test_lookahead_verdict_agrees_with_the_oracle_fallback(opts):
+    """'Cannot fit' is only ever said of partitions the oracle stores raw (the look-ahead is a lower bound), and it is
+    said of every partition of full chunks of random words."""
+    R, D, bp = opts
+    rng = np.random.default_rng(200 + R + 2 * bp)
+    said = 0
+    for trial in range(40):
+        chunks = int(rng.integers(2, 17))
+        tail = int(rng.integers(0, 2)) * int(rng.integers(1, 1024))
+        kind = trial % 4
+        if kind == 0:    # random words
+            x = rng.integers(0, 1 << 32, chunks * 1024 + tail, dtype=np.uint64).astype(np.uint32)
+        elif kind == 1:  # distinct but narrow: fits
+            x = rng.permutation(1 << 15)[: chunks * 1024 + tail].astype(np.uint32)
+        elif kind == 2:  # random first chunks, compressible rest
+            x = np.concatenate([rng.integers(0, 1 << 32, 2048, dtype=np.uint64).astype(np.uint32),
+                                np.zeros((chunks - 2) * 1024 + tail, np.uint32)])
+        else:            # wide deltas in the first chunk only
+            x = np.concatenate([rng.integers(0, 1 << 32, 1024, dtype=np.uint64).astype(np.uint32),
+                                rng.permutation(1 << 12)[:1024].astype(np.uint32),
+                                np.arange((chunks - 2) * 1024 + tail, dtype=np.uint32)])
+        if len(x) < 2048 or distinct_chunk_bytes_model(x[:1024], R, bp) == 0:
+            continue
+        comp = o.casc_compress(x.view(np.uint8), 5, R, D, bp)
+        raw = (comp.view(np.uint32)[0] & 0xFFFFFF) == 0
+        # the encoder only looks ahead when the first chunk itself fitted
+        first_fits = 8 + distinct_chunk_bytes_model(x[:1024], R, bp) <= 8 + 4 * len(x)
+        verdict = first_fits and partition_cannot_fit_model(x, R, bp)
+        if verdict:
+            said += 1
+            assert raw, f"trial {trial}: look-ahead says 'cannot fit' of a partition the oracle compresses"
+        if kind == 0:
+            assert raw
+            if tail == 0:  # (a ragged tail is only counted with its metadata: the bound may fall short)
+                assert verdict or not first_fits
+    assert said > 0
