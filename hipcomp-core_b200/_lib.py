@@ -62,6 +62,7 @@ EXT_PROTOTYPES = {
     "b200compManagerCreateSnappy": [_sz, _vp, C.c_int, _vpp],
     "b200compManagerCreateCascaded": [C.POINTER(CascadedOpts), _vp, C.c_int, _vpp],
     "b200compManagerCreateFromBuffer": [_vp, _vp, C.c_int, _vpp],
+    "b200compManagerSetChecksumMode": [_vp, C.c_int],
     "b200compManagerConfigureCompression": [_vp, _sz, _vpp, _szp, _szp],
     "b200compManagerCompress": [_vp, _vp, _vp, _vp],
     "b200compManagerGetCompressedOutputSize": [_vp, _vp, _szp],

@@ -21,6 +21,7 @@
 // batched decoder -> a status fold into the config's pinned status word.
 #include "common.cuh"
 #include "workspace.hpp"
+#include "crc32.cuh"
 
 #pragma GCC visibility push(default)
 #include "hipcomp/b200_ext.h"
@@ -222,6 +223,7 @@ struct HeaderFill {
   uint8_t format;
   uint64_t decomp_data_size, num_chunks, uncomp_chunk_size;
   uint32_t comp_data_offset;
+  bool checksums; // the per-chunk CRC-32 arrays are filled (b200compManagerSetChecksumMode)
 };
 
 // offsets[i] = cursor + exclusive sum of the (padded) sizes of the wave; cursor += total.
@@ -248,8 +250,8 @@ place_kernel(const size_t* sizes, size_t* offsets, size_t n, unsigned long long*
       h->include_chunk_starts = true;
       h->full_comp_buffer_checksum = 0;
       h->decomp_buffer_checksum = 0;
-      h->include_per_chunk_comp_buffer_checksums = false;
-      h->include_per_chunk_decomp_buffer_checksums = false;
+      h->include_per_chunk_comp_buffer_checksums = hf.checksums;
+      h->include_per_chunk_decomp_buffer_checksums = hf.checksums;
       h->uncomp_chunk_size = hf.uncomp_chunk_size;
       h->comp_data_offset = hf.comp_data_offset;
     }
@@ -517,10 +519,15 @@ public:
     cu_check(cudaMemsetAsync(&header->comp_data_size, 0, sizeof(uint64_t), stream_), "reset comp_data_size");
     size_t* offsets = align8(reinterpret_cast<size_t*>(fmt + format_header_bytes()));
     size_t* sizes = offsets + n;
-    uint8_t* data = reinterpret_cast<uint8_t*>(sizes + n) + 8 * n; // two u32 checksum arrays, never filled
-    cu_check(cudaMemsetAsync(sizes + n, 0, 8 * n, stream_), "zero checksums");
+    // two u32 arrays: CRC-32 of every compressed / uncompressed chunk when checksums are on, else zero (as the
+    // reference leaves them)
+    uint32_t* comp_crc = reinterpret_cast<uint32_t*>(sizes + n);
+    uint32_t* decomp_crc = comp_crc + n;
+    uint8_t* data = reinterpret_cast<uint8_t*>(sizes + n) + 8 * n;
+    const bool crcs = checksum_mode_ != 0;
+    if (!crcs) cu_check(cudaMemsetAsync(sizes + n, 0, 8 * n, stream_), "zero checksums");
 
-    HeaderFill hf{header, format(), cfg.uncompressed_buffer_size, n, chunk_, (uint32_t)(data - comp_buffer)};
+    HeaderFill hf{header, format(), cfg.uncompressed_buffer_size, n, chunk_, (uint32_t)(data - comp_buffer), crcs};
     unsigned long long* cursor = reinterpret_cast<unsigned long long*>(&header->comp_data_size);
     if (n == 0) {
       place_kernel<<<1, 1024, kPlaceSmem, stream_>>>(sizes, offsets, 0, cursor, 1, hf);
@@ -541,6 +548,13 @@ public:
       setup_compress_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(decomp_buffer, cfg.uncompressed_buffer_size, chunk_, start,
                                                                   m, slots, slot_stride_, in_ptrs, in_bytes, out_ptrs);
       batch_compress(in_ptrs, in_bytes, m, temp, temp_bytes, out_ptrs, sizes + start);
+      if (crcs) {
+        const int g = crc_grid(m);
+        b200comp::crc::crc32_chunks_kernel<<<g, b200comp::crc::kWarps * 32, 0, stream_>>>(
+            in_ptrs, in_bytes, m, decomp_crc + start, nullptr, nullptr, nullptr);
+        b200comp::crc::crc32_chunks_kernel<<<g, b200comp::crc::kWarps * 32, 0, stream_>>>(
+            out_ptrs, sizes + start, m, comp_crc + start, nullptr, nullptr, nullptr);
+      }
       if (m <= 8192) {
         place_kernel<<<1, 1024, kPlaceSmem, stream_>>>(sizes + start, offsets + start, m, cursor, chunk_align(), hf);
       } else {
@@ -592,7 +606,11 @@ public:
     const uint8_t* fmt = comp_buffer + sizeof(CommonHeader);
     const size_t* offsets = align8(reinterpret_cast<const size_t*>(fmt + format_header_bytes()));
     const size_t* sizes = offsets + n;
+    const uint32_t* comp_crc = reinterpret_cast<const uint32_t*>(sizes + n);
+    const uint32_t* decomp_crc = comp_crc + n;
     const uint8_t* data = reinterpret_cast<const uint8_t*>(sizes + n) + 8 * n;
+    const CommonHeader* header = reinterpret_cast<const CommonHeader*>(comp_buffer);
+    const bool crcs = checksum_mode_ != 0; // verified where the container's header says it carries them
     scratch_.rewind();
     const void** comp_ptrs = scratch_.reserve<const void*>(dwave_);
     size_t* comp_sizes = scratch_.reserve<size_t>(dwave_);
@@ -605,11 +623,23 @@ public:
       setup_decompress_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(
           data, offsets, sizes, &reinterpret_cast<const CommonHeader*>(comp_buffer)->comp_data_size, decomp_buffer, cfg.decomp_data_size, chunk_, start, m, comp_ptrs, comp_sizes,
           out_ptrs, out_caps, cfg.get_status());
+      if (crcs)
+        b200comp::crc::crc32_chunks_kernel<<<crc_grid(m), b200comp::crc::kWarps * 32, 0, stream_>>>(
+            comp_ptrs, comp_sizes, m, nullptr, comp_crc + start, &header->include_per_chunk_comp_buffer_checksums,
+            cfg.get_status());
       batch_decompress(comp_ptrs, comp_sizes, out_caps, actual, m, out_ptrs, statuses);
       fold_status_kernel<<<grid_for(m, 256), 256, 0, stream_>>>(statuses, m, cfg.get_status());
+      if (crcs)
+        b200comp::crc::crc32_chunks_kernel<<<crc_grid(m), b200comp::crc::kWarps * 32, 0, stream_>>>(
+            out_ptrs, actual, m, nullptr, decomp_crc + start, &header->include_per_chunk_decomp_buffer_checksums,
+            cfg.get_status());
     }
     cu_check(cudaGetLastError(), "decompress launches");
   }
+
+  // 0: the arrays stay zero and are ignored (the reference's behaviour); 1: filled on compress, verified on
+  // decompress (include/hipcomp/b200_ext.h, b200compManagerSetChecksumMode)
+  void set_checksum_mode(int mode) { checksum_mode_ = mode; }
 
   void set_scratch_buffer(uint8_t* new_scratch_buffer) final { scratch_.adopt(new_scratch_buffer, scratch_bytes_); }
   size_t get_required_scratch_buffer_size() final { return scratch_bytes_; }
@@ -647,6 +677,14 @@ private:
     if (!scratch_.valid()) scratch_.acquire(scratch_bytes_, stream_);
   }
 
+  static int crc_grid(size_t m)
+  {
+    const size_t need = (m + b200comp::crc::kWarps - 1) / b200comp::crc::kWarps;
+    const size_t cap = (size_t)b200comp::sm_count() * 8;
+    return (int)(need < cap ? need : cap);
+  }
+
+  int checksum_mode_ = 0;
   CommonHeader* header_host_ = nullptr;
   PinnedPtrPool<hipcompStatus_t> status_pool_;
   b200comp::Workspace scratch_;
@@ -776,6 +814,23 @@ private:
 };
 
 } // namespace
+
+// behind b200compManagerSetChecksumMode (hlif_capi.cu): reaches the batch manager inside a PimplManager
+// (whose `impl` is protected, as in the reference's class)
+namespace {
+struct PimplAccess : PimplManager {
+  static hipcompManagerBase* get(PimplManager* p) { return (p->*(&PimplAccess::impl)).get(); }
+};
+} // namespace
+bool b200_set_checksum_mode(hipcompManagerBase* m, int mode)
+{
+  if (auto* p = dynamic_cast<PimplManager*>(m)) m = PimplAccess::get(p);
+  if (auto* b = dynamic_cast<BatchManager*>(m)) {
+    b->set_checksum_mode(mode);
+    return true;
+  }
+  return false;
+}
 
 LZ4Manager::LZ4Manager(size_t uncomp_chunk_size, hipcompType_t data_type, hipStream_t user_stream, const int device_id)
 {

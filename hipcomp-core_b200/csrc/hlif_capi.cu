@@ -11,6 +11,10 @@
 #include <memory>
 #include <stdexcept>
 
+namespace hipcomp {
+bool b200_set_checksum_mode(hipcompManagerBase* m, int mode); // hlif.cu
+}
+
 struct b200compManager {
   std::shared_ptr<hipcomp::hipcompManagerBase> m;
 };
@@ -64,6 +68,16 @@ hipcompStatus_t b200compManagerCreateFromBuffer(const void* buf, hipStream_t str
                  [&] { *out = new b200compManager{hipcomp::create_manager(static_cast<const uint8_t*>(buf), stream, dev)}; });
 }
 void b200compManagerDestroy(b200compManager* m) { delete m; }
+
+hipcompStatus_t b200compManagerSetChecksumMode(b200compManager* m, int mode)
+{
+  static const char* fn = "b200compManagerSetChecksumMode()";
+  B200_CHECK_NOT_NULL(m, fn);
+  if (mode != 0 && mode != 1) return b200comp::fail(hipcompErrorInvalidValue, fn, "mode must be 0 (none) or 1 (CRC-32 per chunk)");
+  if (!hipcomp::b200_set_checksum_mode(m->m.get(), mode))
+    return b200comp::fail(hipcompErrorNotSupported, fn, "not a manager of this library");
+  return hipcompSuccess;
+}
 
 hipcompStatus_t b200compManagerConfigureCompression(b200compManager* m, size_t bytes, b200compCompConfig** out,
                                                     size_t* max_compressed_bytes, size_t* num_chunks)

@@ -116,6 +116,11 @@ class Manager:
         self._scratch = scratch  # keep it alive
         _ck(L.lib().b200compManagerSetScratchBuffer(self._h, scratch.data_ptr()), "set_scratch_buffer")
 
+    def set_checksum_mode(self, mode):
+        """0: none (the reference's containers); 1: CRC-32 per compressed / uncompressed chunk, filled by compress()
+        and verified by decompress() (extension, include/hipcomp/b200_ext.h)."""
+        _ck(L.lib().b200compManagerSetChecksumMode(self._h, int(mode)), "set_checksum_mode")
+
     def close(self):
         if getattr(self, "_h", None):
             for cfg in list(getattr(self, "_configs", ())):

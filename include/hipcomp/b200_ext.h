@@ -111,6 +111,14 @@ hipcompStatus_t b200compManagerCreateCascaded(const void* opts, hipStream_t stre
 hipcompStatus_t b200compManagerCreateFromBuffer(const void* device_comp_buffer, hipStream_t stream, int device_id,
                                                 b200compManager** out);
 void b200compManagerDestroy(b200compManager* m);
+/* Per-chunk checksums of the container.  The HLIF container reserves a u32 per chunk for the
+ * compressed and for the uncompressed bytes plus two header flags (reference BatchManager.hpp:103-122,213-257); the
+ * reference never fills them and defines no function for them.  mode 1: compress() stores the CRC-32 of zlib
+ * (ISO-HDLC, polynomial 0xEDB88320) of every compressed and every uncompressed chunk and sets the flags;
+ * decompress() recomputes both for containers whose flags are set and reports hipcompErrorCannotDecompress through
+ * the config's status on a mismatch.  mode 0 (default): arrays zero, flags clear, nothing verified - what the
+ * reference writes.  Either kind of container decodes with either mode and with the reference's managers. */
+hipcompStatus_t b200compManagerSetChecksumMode(b200compManager* m, int mode);
 
 hipcompStatus_t b200compManagerConfigureCompression(b200compManager* m, size_t uncompressed_bytes,
                                                     b200compCompConfig** out, size_t* max_compressed_bytes,

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """HLIF (manager) throughput: one buffer in, one self-describing container out, and back.
-usage: bench_hlif.py [size_mib]   - CUDA events on the manager's stream, 3 warm-up + 5 timed calls each way."""
+usage: bench_hlif.py [size_mib] [--checksums]   - CUDA events on the manager's stream, 3 warm-up + 5 timed calls each way."""
 import importlib, json, os, sys
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -16,6 +16,14 @@ cases = [("lz4", lambda: M.LZ4Manager(65536), S.log_lines(n, 0xB202, dev)),
          ("cascaded(1,1,1)", lambda: M.CascadedManager(L.CascadedOpts(4096, L.TYPE_INT, 1, 1, 1)),
           S.sorted_ints(n // 4, 0xB203, dev).view(torch.uint8)),
          ("cascaded(default 2,1,1)", lambda: M.CascadedManager(), S.sorted_ints(n // 4, 0xB203, dev).view(torch.uint8))]
+if "--checksums" in sys.argv:  # the same managers with per-chunk CRC-32 filled on compress and verified on decompress
+    def with_crc(make):
+        def f():
+            m = make()
+            m.set_checksum_mode(1)
+            return m
+        return f
+    cases = [(name + " + crc32", with_crc(make), raw) for name, make, raw in cases[:3]]
 ev = lambda: torch.cuda.Event(enable_timing=True)
 for name, make, raw in cases:
     mgr = make()
