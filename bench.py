@@ -588,6 +588,23 @@ def measure_codec(args, codec, world, rank, local, device, with_cpu):
 CASCADED_LAUNCHES_PER_STEP = 6  # 1 compress + 5 decompress instantiations (4 exit after reading partition 0's header)
 
 
+def cascaded_default_options(args, world, rank, local, device):
+    """The C3 column once more (1 GiB) with the library's default Cascaded options (num_RLEs 2, num_deltas 1,
+    bit-packed) - the same call `--codec cascaded --casc-opts 2,1,1 --size-mib 1024 --no-e2e --no-cpu` makes, so that
+    the default run's record carries it.  Device-timed only, N = 1 only; never allowed to break the headline line."""
+    if world != 1 or args.impl != "b200" or args.casc_opts != "1,1,1" or args.casc_type != "int" or args.data != "default":
+        return None
+    try:
+        sub = argparse.Namespace(**vars(args))
+        sub.casc_opts, sub.size_mib, sub.no_e2e = "2,1,1", 1024, True
+        rec = measure_codec(sub, "cascaded", world, rank, local, device, False)
+        keep = ("config", "ms_per_step", "compress_GBps", "decompress_GBps", "compression_ratio", "roofline_compress",
+                "roofline_decompress", "gpu_launches")
+        return {"value": rec["value"], **{k: rec[k] for k in keep}}
+    except Exception as e:  # noqa: BLE001 - an auxiliary record
+        return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+
 def run_b200(args):
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
     world, rank, local = dist_setup(args.gpus)
@@ -614,6 +631,9 @@ def run_b200(args):
             line[k] = head[k]
     if len(codecs) > 1:
         line["codecs"] = {c: recs[c] for c in codecs[1:]}
+        extra = cascaded_default_options(args, world, rank, local, device)
+        if extra is not None and line["codecs"].get("cascaded") is not None:
+            line["codecs"]["cascaded"]["default_options"] = extra
     print(json.dumps(line), flush=True)
 
 

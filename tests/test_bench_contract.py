@@ -48,3 +48,38 @@ def test_reference_arm_runs_without_a_gpu():
     assert line["impl"] == "reference" and line["unit"] == "GB/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
+
+
+def test_default_options_subrecord_is_auxiliary():
+    """codecs.cascaded.default_options: the (2,1,1) invocation's arguments, a subset of its record, N = 1 only, and an
+    exception inside it never reaches the headline line."""
+    b = _bench()
+    argv, sys.argv = sys.argv, ["bench.py"]
+    try:
+        args = b.parse_args()
+    finally:
+        sys.argv = argv
+    seen = {}
+
+    def fake(sub, codec, world, rank, local, device, with_cpu):
+        seen.update(casc_opts=sub.casc_opts, size_mib=sub.size_mib, no_e2e=sub.no_e2e, codec=codec, with_cpu=with_cpu)
+        wl = b.workload_for(sub, codec)
+        return {"value": 1.0, "config": b.make_config(wl, world, sub.size_mib << 20, 1), "ms_per_step": 1.0,
+                "compress_GBps": 2.0, "decompress_GBps": 3.0, "compression_ratio": 7.0, "roofline_compress": {},
+                "roofline_decompress": {}, "gpu_launches": 6, "clocks": {}, "e2e": {"never": "copied"}}
+
+    real, b.measure_codec = b.measure_codec, fake
+    try:
+        rec = b.cascaded_default_options(args, 1, 0, 0, None)
+        assert seen == dict(casc_opts="2,1,1", size_mib=1024, no_e2e=True, codec="cascaded", with_cpu=False)
+        assert args.casc_opts == "1,1,1" and not args.no_e2e, "the caller's arguments are untouched"
+        assert rec["compress_GBps"] == 2.0 and "opts 2,1,1" in rec["config"]["workload"] and "e2e" not in rec
+        assert b.cascaded_default_options(args, 2, 0, 0, None) is None
+
+        def boom(*a, **k):
+            raise RuntimeError("no device")
+
+        b.measure_codec = boom
+        assert "RuntimeError" in b.cascaded_default_options(args, 1, 0, 0, None)["error"]
+    finally:
+        b.measure_codec = real
