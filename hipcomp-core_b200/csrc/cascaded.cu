@@ -15,6 +15,16 @@
 //            compile-time bit widths (no per-element shift bookkeeping)
 // An SM keeps up to 32 independent partitions in flight with no block barrier.
 // Grids are persistent (multiple of the SM count) and grid-stride over the batch.
+//
+// Fused paths for 4-byte elements on full, 16-byte aligned chunks (same bytes as the generic layer loop):
+//   encode  num_RLEs 1 or 2, num_deltas 1: compress_chunk_rd1 - run flags from registers, only compacted
+//           (value, end) pairs touch shared memory; for num_RLEs 2 the second layer is rle_encode_minmax.
+//           Partitions whose first chunk turns out all distinct are sized ahead (partition_cannot_fit)
+//           and stored raw at once when they cannot fit.
+//   decode  num_RLEs 1: decompress_chunk_r1d1; num_RLEs 2 (library default): decompress_chunk_r2d1;
+//           any deeper stack that ends in (first RLE, one delta): decompress_tail_d1 behind the generic layers.
+//           All three stage the stream in shared memory, scatter deltas onto run starts of a zeroed array and
+//           finish with one register prefix sum over the 1024 outputs.
 #include "common.cuh"
 
 #include <type_traits>
