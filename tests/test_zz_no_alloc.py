@@ -118,7 +118,7 @@ def test_noalloc_full_batch_typed_and_no_device_allocation():
     torch.cuda.synchronize()
     free_after, _ = torch.cuda.mem_get_info()
     assert st == L.SUCCESS
-    assert free_after == free_before
+    assert free_after >= free_before, "the call allocated device memory"
     _assert_same_streams(got, want)
 
 
