@@ -125,3 +125,17 @@ def test_team_model_ratio_not_below_reference_policy():
         assert team <= ref * 1.01
     z = np.zeros(65536, np.uint8)
     assert len(o.lz4_team_compress(z, 65536)) == len(o.lz4_compress(z, 1, 65536))  # runs merge across segments
+
+
+def test_maximum_chunk_size_of_the_format():
+    """16 MiB, the largest chunk the C ABI accepts (reference LZ4Batch.cpp:154-170): the reference-policy oracle's stream
+    for one such chunk decodes with liblz4 and with the oracle's own decoder, and stays inside GetMaxOutputChunkSize."""
+    n = 1 << 24
+    raw = np.resize(datagen.log_lines(1 << 20, 31), n).copy()
+    raw[5 << 20:6 << 20] = np.random.default_rng(3).integers(0, 256, 1 << 20, dtype=np.uint8)  # an incompressible stretch
+    comp = o.lz4_compress(raw, 1, n)
+    assert len(comp) <= o.lz4_max_compressed(n)
+    m, out = stock_decompress(comp, n)
+    assert m == n and out.tobytes() == raw.tobytes()
+    st, back = o.lz4_decompress(comp, n)
+    assert st == 0 and back.tobytes() == raw.tobytes()
