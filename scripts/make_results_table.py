@@ -83,8 +83,9 @@ def main():
                    f"{cd.get('cascaded', {}).get('value', float('nan')):.0f} | {c4['value'] if c4 else float('nan'):.0f} | "
                    f"{(c4 or {}).get('size_gather_ms') or 0:.1f} | {ccn.get('duplex_GBps_each_way', float('nan')):.0f} | "
                    f"{rf['value'] if rf else float('nan'):.2f} ({rf['cpu_baseline']['cores'] if rf else '?'} cores) |")
-    out.append("\n(N = 1, 2, 8: the closing library.  N = 4: records of the library before the last decoder and Cascaded changes "
-               "(DESIGN §6 r2m-r2q) - Snappy decode 152 instead of 174 GB/s per GPU, Cascaded default options slower; LZ4 unchanged.)")
+    out.append("\n(N = 1, 2, 8: the closing library.  N = 4, here and in 5c: records of the library before the last decoder and Cascaded changes "
+               "(DESIGN §6 r2m-r2q) - Snappy decode 152 instead of 174 GB/s per GPU, Cascaded random-class compress 0.55 instead of 1.8 TB/s per GPU; "
+               "LZ4 unchanged.)")
     # C5
     out.append("\n### 5c. C5 input-class sweep (16 GiB per class for the whole job; compress / decompress GB/s, ratio)\n")
     for n in (1, 2, 4, 8):
