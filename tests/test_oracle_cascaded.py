@@ -245,3 +245,65 @@ def test_lookahead_verdict_agrees_with_the_oracle_fallback(opts):
             if tail == 0:  # (a ragged tail is only counted with its metadata: the bound may fall short)
                 assert verdict or not first_fits
     assert said > 0
+
+
+# ---- the GPU decoder's formulation for the default options (csrc/cascaded.cu: decompress_chunk_r2d1 +
+# decompress_tail_d1) restated in numpy on the oracle's streams: both run-length layers expand by "scatter onto run
+# starts, then one running sum" instead of marking and gathering.
+def unpack_bp(words, elem_bits):
+    """one bit-packed array of the format: frame of reference, (width << 16 | count), packed words"""
+    fr, meta = int(words[0]), int(words[1])
+    bw, n = meta >> 16, meta & 0xFFFF
+    bits = np.unpackbits(words[2:].view(np.uint8), bitorder="little")
+    vals = np.zeros(n, np.uint64)
+    for b in range(bw):
+        vals |= bits[b:n * bw:bw].astype(np.uint64)[:n] << np.uint64(b) if bw else 0
+    return ((vals + np.uint64(fr)) & np.uint64((1 << elem_bits) - 1)).astype(np.uint64)
+
+
+def decode_chunk_r2d1_model(w):
+    """w: the uint32 words of one (2,1,1) chunk (metadata first) -> its 1024 uint32 outputs"""
+    cb1, cb2, vb, seed = int(w[1]), int(w[2]), int(w[3]), int(w[4])
+    a1, a2, av = 5, 5 + cb1 // 4, 5 + cb1 // 4 + cb2 // 4
+    len1 = unpack_bp(w[a1:a1 + cb1 // 4], 16).astype(np.int64)
+    len2 = unpack_bp(w[a2:a2 + cb2 // 4], 16).astype(np.int64)
+    val2 = unpack_bp(w[av:av + vb // 4], 32).astype(np.int64)
+    n2 = len(val2)
+    len2 = len2[:n2]
+    assert (len2 >= 1).all()
+    # layer 2: run k stores val2[k] - val2[k-1] at its start; the running sum is the delta array
+    nv = int(len2.sum())
+    e = np.zeros(nv, np.int64)
+    starts2 = np.cumsum(len2) - len2
+    e[starts2] = np.diff(val2, prepend=0)
+    deltas = np.cumsum(e) & 0xFFFFFFFF
+    # layer 1 + delta: run j adds its delta (the seed for run 0) at its start; the running sum is the output
+    m = nv + 1
+    starts1 = (np.cumsum(len1[:m]) - len1[:m])
+    assert int(len1[:m].sum()) == 1024
+    o_ = np.zeros(1024, np.int64)
+    np.add.at(o_, starts1, np.concatenate([[seed], deltas]))
+    return (np.cumsum(o_) & 0xFFFFFFFF).astype(np.uint32)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_default_options_decoder_formulation(seed):
+    import datagen
+
+    rng = np.random.default_rng(seed)
+    cols = [datagen.sorted_ints(4096, seed).astype(np.uint32),
+            np.repeat(rng.integers(0, 1 << 20, 300), rng.integers(1, 30, 300))[:4096].astype(np.uint32),
+            np.cumsum(np.repeat(rng.integers(1, 5, 700), rng.integers(1, 12, 700))[:4096]).astype(np.uint32),
+            np.zeros(4096, np.uint32),
+            (np.arange(4096) // 3 * 7).astype(np.uint32)]
+    for x in cols:
+        assert len(x) == 4096
+        comp = o.casc_compress(x.view(np.uint8), 5, 2, 1, 1)
+        w = comp.view(np.uint32)
+        assert (w[0] & 0xFFFFFF) == (2 | 1 << 8 | 1 << 16), "stays compressed"
+        pos, out = 2, []
+        while pos < len(w):
+            nbytes = int(w[pos])
+            out.append(decode_chunk_r2d1_model(w[pos:pos + nbytes // 4]))
+            pos += nbytes // 4
+        assert np.array_equal(np.concatenate(out), x)
